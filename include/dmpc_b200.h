@@ -1,0 +1,149 @@
+/*
+ * dmpc_b200.h - C ABI of the B200-native LPV-MPC QP path.
+ *
+ * The reference (MarcFacerias/ColaborativeMPC-) has no FFI layer: its boundary for this path is the
+ * Python object API  PlannerLPV(...).solve(...)  (planner/lib/plan_lib/distributedPlanner/LPV_Planner.py:17,
+ * :115-182) called from  agent.one_step  (planner/scripts/LPV_HP_N_main.py:41) and the neighbour exchange of
+ * planner/scripts/LPV_HP_N_main.py:117.  The entry points below are what a ctypes binding for that path
+ * binds; colaborativempc_b200/planner.py is that binding.
+ *
+ * Conventions: plain pointers and sizes, no torch types.  All `d_*` pointers are DEVICE pointers owned by the
+ * caller, all `h_*` pointers are HOST pointers owned by the caller.  Every function returns 0 on success or a
+ * negative dmpc_error; dmpc_last_error() gives text.  A handle is bound to one device and one stream user at
+ * a time (not thread-safe, like the reference controller object, which mutates self.*).
+ */
+#ifndef DMPC_B200_H
+#define DMPC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DMPC_NS 9          /* states  [vx vy psidot e_y e_psi theta s x y]  (plan_lib/config/__init__.py:4) */
+#define DMPC_NSLACK 3      /* slacks per stage                               (LPV_Planner.py:20-23)          */
+#define DMPC_NEXP 12
+#define DMPC_NU 2
+#define DMPC_MAX_SEG 32    /* rows of Map.PointAndTangent kept per lane      (track_initialization.py:98-300)  */
+
+/* Constructor arguments of PlannerLPV (LPV_Planner.py:17-105) + the map table read by
+ * curvature()/get_ey() (utilities/misc.py:78-126). */
+typedef struct dmpc_params {
+  int32_t N;              /* horizon                                                         */
+  int32_t nn;             /* neighbour slots per agent (len(agents_id) of the first call)    */
+  int32_t nseg;           /* map segments                                                    */
+  int32_t reserved;
+  double dt, wq;
+  double Q[81];           /* row-major 9x9                                                   */
+  double Qs[9];           /* row-major 3x3                                                   */
+  double R[4];
+  double dR[4];
+  double lf, lr, m, I, Cf, Cr, mu;                                     /* model_param        */
+  double vx_ref, min_dist, max_vel, min_vel, max_rs, max_ls, max_ac, max_dc; /* sys_lim      */
+  double seg_s0[DMPC_MAX_SEG];   /* PointAndTangent[:,3,lane]                                */
+  double seg_len[DMPC_MAX_SEG];  /* PointAndTangent[:,4,lane]                                */
+  double seg_curv[DMPC_MAX_SEG]; /* PointAndTangent[:,5,lane]                                */
+  double seg_hw[DMPC_MAX_SEG];   /* halfWidth[:]                                             */
+} dmpc_params;
+
+/* Solver options.  Defaults (dmpc_default_options) follow what osqp_solve_qp passes
+ * (LPV_Planner.py:233: polish=True, max_iter=500000) and OSQP's documented defaults. */
+typedef struct dmpc_options {
+  double rho;             /* 0.1                                                             */
+  double sigma;           /* 1e-6                                                            */
+  double alpha;           /* 1.6                                                             */
+  double eps_abs, eps_rel;/* ADMM stopping tolerance before polish (1e-3, 1e-3)              */
+  int32_t max_iter;       /* total ADMM iterations per QP before status -2                    */
+  int32_t check_every;    /* termination / adaptive-rho period (25)                          */
+  int32_t polish;         /* 1: active-set polish + KKT certificate (exact optimum)          */
+  int32_t polish_max_pivots; /* active-set correction rounds per polish attempt              */
+  double cert_tol;        /* KKT certificate tolerance (relative), 1e-9                      */
+} dmpc_options;
+
+/* Per-QP status values mirror OSQP's status_val so `feasible` is derived as LPV_Planner.py:246-248. */
+enum dmpc_status {
+  DMPC_SOLVED = 1,
+  DMPC_SOLVED_INACCURATE = 2,
+  DMPC_MAX_ITER_REACHED = -2,
+  DMPC_PRIMAL_INFEASIBLE = -3,
+  DMPC_DUAL_INFEASIBLE = -4,
+  DMPC_MAP_LOOKUP_FAILED = -20, /* curvature()/get_ey() find no segment (misc.py:97: int() of an empty index raises) */
+  DMPC_DEGENERATE_PLANE = -21,  /* ego and neighbour coincide: compute_plane.py:52 divides by zero        */
+  DMPC_UNSOLVED = -10
+};
+
+enum dmpc_error {
+  DMPC_OK = 0,
+  DMPC_ERR_ARG = -1,
+  DMPC_ERR_CUDA = -2,
+  DMPC_ERR_UNSUPPORTED = -3,
+  DMPC_ERR_NOMEM = -4
+};
+
+/* One batch of B independent agent QPs (B = scenarios x local agents).  Layouts are the reference's numpy
+ * layouts with a leading batch axis, C-contiguous FP64. */
+typedef struct dmpc_batch_io {
+  int32_t B;
+  int32_t xprev_rows;        /* N+1 on the first DMPC iteration, N afterwards (LPV_HP_N_main.py:114-115) */
+  /* inputs */
+  const double* x0;          /* [B,9]                 solve(x0, ...)                                   */
+  const double* xprev;       /* [B,xprev_rows,9]      Last_xPredicted                                  */
+  const double* uprev;       /* [B,N,2]               uPred                                            */
+  const double* uold;        /* [B,2]                 (OldSteering[0], OldAccelera[0]) :153            */
+  const double* nbr_xy;      /* [B,N+1,nn,2]          x_agents                                         */
+  const double* pose;        /* [B,N+1,2]             pose (ego predicted x,y)                          */
+  const int32_t* nbr_count;  /* [B] or NULL (= nn for all); rows beyond the count are left out of the QP */
+  /* outputs (any may be NULL) */
+  double* z;                 /* [B,16N+12]            Solution = res.x                      :162        */
+  double* planes;            /* [B,N,3,nn]            :138                                              */
+  double* y_ineq;            /* [B,(8+nn)N]           multipliers of the rows of F (first rows of res.y) */
+  double* y_eq;              /* [B,14N+12]            multipliers of the rows of G (adjoint recursion)   */
+  double* obj;               /* [B]                   res.info.obj_val                                  */
+  int32_t* status;           /* [B]                   res.info.status_val                               */
+  int32_t* iters;            /* [B]                   ADMM iterations used                               */
+  int32_t* pivots;           /* [B]                   active-set polish rounds used                      */
+} dmpc_batch_io;
+
+typedef struct dmpc_handle dmpc_handle;
+
+void dmpc_default_options(dmpc_options* opt);
+int dmpc_version(void);
+
+/* device < 0: current device.  max_batch sizes the handle-owned workspaces. */
+int dmpc_create(const dmpc_params* params, const dmpc_options* opt, int32_t max_batch, int32_t device,
+                dmpc_handle** out);
+void dmpc_destroy(dmpc_handle* h);
+const char* dmpc_last_error(const dmpc_handle* h);
+int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt);
+
+/* Replaces steps 2-9 of PlannerLPV.solve (LPV_Planner.py:138-180) for B QPs with DEVICE buffers.
+ * `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  Asynchronous. */
+int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* stream);
+
+/* Same call with HOST buffers: pinned staging + H2D, solve, D2H inside (the end-to-end path). Synchronous. */
+int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io);
+
+/* Caller-side bookkeeping of one DMPC iteration (LPV_HP_N_main.py:106,113-117), on device:
+ *   x0 <- xPred[1];  xprev <- xPred[1:] (N rows);  uprev <- uPred;  uold <- uPred[0];
+ *   xy_send[b,t,:] = xPred[b,t,7:9]  (packed for the neighbour exchange).
+ * z is [B,16N+12]; outputs may alias nothing in z. */
+int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, double* d_x0, double* d_xprev /*[B,N,9]*/,
+                    double* d_uprev, double* d_uold, double* d_xy_send /*[B,N+1,2]*/, void* stream);
+
+/* After the exchange: gathers each agent's neighbour trajectories and its own pose from the all-gathered
+ * buffer  xy_all [S, A, N+1, 2]  (scenario-major, A agents per scenario):
+ *   nbr_xy[b,t,j,:] = xy_all[s(b), nbr_idx[b,j], t, :],  pose[b,t,:] = xy_all[s(b), a(b), t, :]
+ * where local QP b = (s_local * A_local + a_local), global agent a(b) = agent_offset + a_local.
+ * nbr_idx is [A_local? no: B, nn] int32 of global agent ids (agents_id of the reference), -1 = empty slot. */
+int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
+                           const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
+                           void* stream);
+
+/* Number of kernels the handle has launched so far (bench.py's gpu_launches claim). */
+int64_t dmpc_launch_count(const dmpc_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DMPC_B200_H */
