@@ -33,7 +33,7 @@ class OracleIO(C.Structure):
 def build(force=False):
     if force or not os.path.exists(LIB) or any(
             os.path.getmtime(os.path.join(HERE, f)) > os.path.getmtime(LIB)
-            for f in ("lpv_oracle.c", "osqp_restated.inc", "api.inc")):
+            for f in ("lpv_oracle.c", "osqp_restated.inc", "exact_ipm.inc", "api.inc")):
         subprocess.check_call(["make", "-C", HERE, "-B", "-s"])
     return LIB
 
