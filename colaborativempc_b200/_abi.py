@@ -36,10 +36,9 @@ class DmpcParams(C.Structure):
 
 class DmpcOptions(C.Structure):
     _fields_ = [
-        ("rho", C.c_double), ("sigma", C.c_double), ("alpha", C.c_double),
-        ("eps_abs", C.c_double), ("eps_rel", C.c_double),
-        ("max_iter", C.c_int32), ("check_every", C.c_int32), ("polish", C.c_int32),
-        ("polish_max_pivots", C.c_int32), ("cert_tol", C.c_double),
+        ("polish_delta", C.c_double), ("cert_tol", C.c_double), ("ipm_mu0", C.c_double),
+        ("polish_refine", C.c_int32), ("pdas_first", C.c_int32), ("pdas_after", C.c_int32),
+        ("ipm_max_iter", C.c_int32), ("reserved0", C.c_int32), ("reserved1", C.c_int32),
     ]
 
 

@@ -1,0 +1,314 @@
+// dmpc_api.cu - C ABI (include/dmpc_b200.h) over the sm_100a kernels.  No torch types, no CPU compute path:
+// every numeric result comes from lpv_qp_solve_kernel / the bookkeeping kernels below.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "qp_kernel.cuh"
+
+struct dmpc_handle {
+  dmpc_params params;
+  dmpc_options opt;
+  DevParams P;
+  int device, max_batch, smem_limit;
+  size_t smem_bytes;
+  long long gws_stride;
+  double* d_gws;
+  // staging for the host-buffer entry point
+  char* d_stage;
+  size_t stage_bytes;
+  int64_t launches;
+  char err[256];
+};
+
+static int fail(dmpc_handle* h, int code, const char* fmt, const char* a = "") {
+  if (h) snprintf(h->err, sizeof(h->err), fmt, a);
+  return code;
+}
+#define CUDA_TRY(h, call)                                                         \
+  do {                                                                            \
+    cudaError_t e_ = (call);                                                      \
+    if (e_ != cudaSuccess) return fail((h), DMPC_ERR_CUDA, "CUDA: %s", cudaGetErrorString(e_)); \
+  } while (0)
+
+extern "C" int dmpc_version(void) { return 100; }
+
+extern "C" void dmpc_default_options(dmpc_options* o) {
+  if (!o) return;
+  o->polish_delta = 1e-9; o->cert_tol = 1e-9; o->ipm_mu0 = 1e-6;
+  o->polish_refine = 4; o->pdas_first = 6; o->pdas_after = 4; o->ipm_max_iter = 60;
+  o->reserved0 = o->reserved1 = 0;
+}
+
+static void apply_options(dmpc_handle* h) {
+  h->P.delta = h->opt.polish_delta; h->P.cert_tol = h->opt.cert_tol; h->P.ipm_mu0 = h->opt.ipm_mu0;
+  h->P.refine = h->opt.polish_refine; h->P.pdas_first = h->opt.pdas_first; h->P.pdas_after = h->opt.pdas_after;
+  h->P.ipm_max = h->opt.ipm_max_iter;
+}
+
+static bool options_ok(const dmpc_options* o) {
+  return o->polish_delta > 0 && o->polish_delta < 1e-3 && o->cert_tol > 0 && o->ipm_mu0 > 0 && o->polish_refine >= 0 &&
+         o->polish_refine <= 32 && o->pdas_first >= 0 && o->pdas_after >= 1 && o->ipm_max_iter >= 1;
+}
+
+// symmetric matrix as OSQP sees it: the upper triangle of the user's array (LPV_Planner.py:156 hands csr(M), and
+// OSQP reads triu(P)).
+static double sym_up(const double* M, int n, int i, int j) { return i <= j ? M[i * n + j] : M[j * n + i]; }
+
+static bool psd(const double* M, int n, bool strict) {  // LDL' without pivoting on the symmetrised matrix
+  double a[81];
+  double scale = 0;
+  for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) { a[i * n + j] = sym_up(M, n, i, j); scale = fmax(scale, fabs(a[i * n + j])); }
+  if (!(scale < 1e300)) return false;
+  const double tol = 1e-12 * (scale > 0 ? scale : 1.0);
+  for (int k = 0; k < n; ++k) {
+    const double d = a[k * n + k];
+    if (strict ? !(d > tol) : !(d >= -tol)) return false;
+    if (d <= tol) {  // zero pivot: the rest of the column must vanish
+      for (int i = k + 1; i < n; ++i) if (fabs(a[i * n + k]) > 1e-9 * (scale + 1)) return false;
+      continue;
+    }
+    for (int i = k + 1; i < n; ++i) {
+      const double l = a[i * n + k] / d;
+      for (int j = k + 1; j < n; ++j) a[i * n + j] -= l * a[k * n + j];
+    }
+  }
+  return true;
+}
+
+extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_t max_batch, int32_t device, dmpc_handle** out) {
+  if (!p || !out) return DMPC_ERR_ARG;
+  *out = nullptr;
+  dmpc_handle* h = new (std::nothrow) dmpc_handle();
+  if (!h) return DMPC_ERR_NOMEM;
+  memset(h, 0, sizeof(*h));
+  *out = h;  // returned even on failure so that dmpc_last_error() can be read; caller destroys it
+  if (p->N < 1 || p->N > 512 || p->nn < 0 || p->nn > 255 || p->nseg < 1 || p->nseg > DMPC_MAX_SEG || !(p->dt > 0) || max_batch < 1)
+    return fail(h, DMPC_ERR_ARG, "bad N/nn/nseg/dt/max_batch%s");
+  if (!psd(p->Q, 9, false) || !psd(p->R, 2, false) || !psd(p->dR, 2, false))
+    return fail(h, DMPC_ERR_ARG, "Q, R and dR must be positive semidefinite%s");
+  if (!psd(p->Qs, 3, true)) return fail(h, DMPC_ERR_ARG, "Qs must be positive definite%s");
+  {
+    double rs[4];
+    for (int i = 0; i < 4; ++i) rs[i] = p->R[i] + p->dR[i];
+    if (!psd(rs, 2, true)) return fail(h, DMPC_ERR_ARG, "R + dR must be positive definite (strictly convex inputs)%s");
+  }
+  h->params = *p;
+  if (opt) h->opt = *opt; else dmpc_default_options(&h->opt);
+  if (!options_ok(&h->opt)) return fail(h, DMPC_ERR_ARG, "bad options%s");
+  if (device < 0) CUDA_TRY(h, cudaGetDevice(&device));
+  h->device = device;
+  CUDA_TRY(h, cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(h, cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return fail(h, DMPC_ERR_UNSUPPORTED, "this library is built for sm_100a (B200) only%s");
+  h->max_batch = max_batch;
+
+  DevParams& P = h->P;
+  P.N = p->N; P.nn = p->nn; P.nseg = p->nseg;
+  P.dt = p->dt; P.wq = p->wq; P.Q00 = p->Q[0];
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) P.Qs[i * 3 + j] = sym_up(p->Qs, 3, i, j);
+  for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) { P.R[i * 2 + j] = sym_up(p->R, 2, i, j); P.dR[i * 2 + j] = sym_up(p->dR, 2, i, j); }
+  P.lf = p->lf; P.lr = p->lr; P.m = p->m; P.I = p->I; P.Cf = p->Cf; P.Cr = p->Cr; P.mu = p->mu;
+  P.vx_ref = p->vx_ref; P.min_dist = p->min_dist; P.max_vel = p->max_vel; P.min_vel = p->min_vel;
+  P.max_rs = p->max_rs; P.max_ls = p->max_ls; P.max_ac = p->max_ac; P.max_dc = p->max_dc;
+  for (int i = 0; i < DMPC_MAX_SEG; ++i) { P.seg_s0[i] = p->seg_s0[i]; P.seg_len[i] = p->seg_len[i]; P.seg_curv[i] = p->seg_curv[i]; P.seg_hw[i] = p->seg_hw[i]; }
+  // state rows kept on chip: the four constrained outputs first, then every other state the cost touches
+  int pos[9];
+  for (int a = 0; a < 9; ++a) pos[a] = -1;
+  const int base[4] = {0, 3, 7, 8};
+  P.nrows = 0;
+  for (int i = 0; i < 4; ++i) { pos[base[i]] = P.nrows; P.rowsel[P.nrows++] = base[i]; }
+  for (int a = 0; a < 9; ++a) {
+    bool used = false;
+    for (int b = 0; b < 9; ++b) used |= (sym_up(p->Q, 9, a, b) != 0.0);
+    if (used && pos[a] < 0) { pos[a] = P.nrows; P.rowsel[P.nrows++] = a; }
+  }
+  P.nq = 0;
+  for (int a = 0; a < 9; ++a) for (int b = a; b < 9; ++b) {
+    const double v = sym_up(p->Q, 9, a, b);
+    if (v != 0.0) { P.qa[P.nq] = pos[a]; P.qb[P.nq] = pos[b]; P.qv[P.nq] = v; ++P.nq; }
+  }
+  apply_options(h);
+
+  // workspace placement: shared memory first, long horizons spill the big blocks to an L2-resident global slice
+  int optin = 0;
+  CUDA_TRY(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+  h->smem_limit = optin;
+  Ctx c;
+  bool placed = false;
+  for (int mode = 0; mode < 3 && !placed; ++mode) {
+    P.gr_global = mode >= 1; P.hk_global = mode >= 2;
+    long long gd = 0;
+    const size_t sb = carve_workspace(c, nullptr, nullptr, P.N, P.nn, P.nrows, P.gr_global, P.hk_global, &gd);
+    if (sb + 64 <= (size_t)optin) { h->smem_bytes = sb + 16; h->gws_stride = (gd + 1) & ~1LL; placed = true; }
+  }
+  if (!placed) return fail(h, DMPC_ERR_UNSUPPORTED, "horizon/neighbour count too large for the on-chip workspace%s");
+  if (h->gws_stride > 0) CUDA_TRY(h, cudaMalloc(&h->d_gws, (size_t)h->gws_stride * sizeof(double) * max_batch));
+  CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+  return DMPC_OK;
+}
+
+extern "C" void dmpc_destroy(dmpc_handle* h) {
+  if (!h) return;
+  if (h->d_gws) cudaFree(h->d_gws);
+  if (h->d_stage) cudaFree(h->d_stage);
+  delete h;
+}
+
+extern "C" const char* dmpc_last_error(const dmpc_handle* h) { return h ? h->err : "null handle"; }
+
+extern "C" int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt) {
+  if (!h || !opt) return DMPC_ERR_ARG;
+  if (!options_ok(opt)) return fail(h, DMPC_ERR_ARG, "bad options%s");
+  h->opt = *opt;
+  apply_options(h);
+  return DMPC_OK;
+}
+
+extern "C" int64_t dmpc_launch_count(const dmpc_handle* h) { return h ? h->launches : 0; }
+
+extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* stream) {
+  if (!h || !io) return DMPC_ERR_ARG;
+  if (io->B == 0) return DMPC_OK;
+  if (io->B < 0 || io->B > h->max_batch) return fail(h, DMPC_ERR_ARG, "batch larger than max_batch%s");
+  if (io->xprev_rows < h->P.N) return fail(h, DMPC_ERR_ARG, "Last_xPredicted needs at least N rows%s");
+  if (!io->x0 || !io->xprev || !io->uprev || !io->uold || !io->pose || (h->P.nn > 0 && !io->nbr_xy))
+    return fail(h, DMPC_ERR_ARG, "null input pointer%s");
+  BatchPtrs bp;
+  bp.B = io->B; bp.xprev_rows = io->xprev_rows;
+  bp.x0 = io->x0; bp.xprev = io->xprev; bp.uprev = io->uprev; bp.uold = io->uold; bp.nbr_xy = io->nbr_xy; bp.pose = io->pose;
+  bp.nbr_count = io->nbr_count;
+  bp.z = io->z; bp.planes = io->planes; bp.y_ineq = io->y_ineq; bp.y_eq = io->y_eq; bp.obj = io->obj;
+  bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
+  bp.gws = h->d_gws; bp.gws_stride = h->gws_stride;
+  lpv_qp_solve_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+  h->launches++;
+  CUDA_TRY(h, cudaGetLastError());
+  return DMPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Host-buffer entry point: H2D of the inputs, solve, D2H of the outputs, all inside the call.
+extern "C" int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io) {
+  if (!h || !io) return DMPC_ERR_ARG;
+  if (io->B == 0) return DMPC_OK;
+  if (io->B < 0 || io->B > h->max_batch) return fail(h, DMPC_ERR_ARG, "batch larger than max_batch%s");
+  const int N = h->P.N, nn = h->P.nn, B = io->B, rows = io->xprev_rows;
+  if (rows < N) return fail(h, DMPC_ERR_ARG, "Last_xPredicted needs at least N rows%s");
+  const size_t n = 16 * (size_t)N + 12, mi = (8 + (size_t)nn) * N, me = 14 * (size_t)N + 12;
+  const size_t Bm = (size_t)h->max_batch;
+  // fixed staging layout sized for max_batch (offsets in bytes, 256-aligned)
+  size_t off = 0;
+  auto seg = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+  const size_t o_x0 = seg(Bm * 9 * 8), o_xp = seg(Bm * (N + 1) * 9 * 8), o_up = seg(Bm * N * 2 * 8), o_uo = seg(Bm * 2 * 8);
+  const size_t o_nb = seg(Bm * (N + 1) * (nn > 0 ? nn : 1) * 2 * 8), o_po = seg(Bm * (N + 1) * 2 * 8), o_nc = seg(Bm * 4);
+  const size_t o_z = seg(Bm * n * 8), o_pl = seg(Bm * N * 3 * (nn > 0 ? nn : 1) * 8), o_yi = seg(Bm * mi * 8), o_ye = seg(Bm * me * 8);
+  const size_t o_ob = seg(Bm * 8), o_st = seg(Bm * 4), o_it = seg(Bm * 4), o_pv = seg(Bm * 4);
+  if (!h->d_stage) {
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    CUDA_TRY(h, cudaMalloc(&h->d_stage, off));
+    h->stage_bytes = off;
+  }
+  if (rows > N + 1) return fail(h, DMPC_ERR_ARG, "Last_xPredicted has more than N+1 rows%s");
+  char* d = h->d_stage;
+  cudaStream_t s = 0;
+#define H2D(dst_off, src, bytes) do { if (src) CUDA_TRY(h, cudaMemcpyAsync(d + (dst_off), (src), (bytes), cudaMemcpyHostToDevice, s)); } while (0)
+#define D2H(dst, src_off, bytes) do { if (dst) CUDA_TRY(h, cudaMemcpyAsync((dst), d + (src_off), (bytes), cudaMemcpyDeviceToHost, s)); } while (0)
+  H2D(o_x0, io->x0, (size_t)B * 9 * 8); H2D(o_xp, io->xprev, (size_t)B * rows * 9 * 8); H2D(o_up, io->uprev, (size_t)B * N * 2 * 8);
+  H2D(o_uo, io->uold, (size_t)B * 2 * 8); H2D(o_nb, io->nbr_xy, (size_t)B * (N + 1) * nn * 2 * 8); H2D(o_po, io->pose, (size_t)B * (N + 1) * 2 * 8);
+  H2D(o_nc, io->nbr_count, (size_t)B * 4);
+  dmpc_batch_io dio = *io;
+  dio.x0 = (const double*)(d + o_x0); dio.xprev = (const double*)(d + o_xp); dio.uprev = (const double*)(d + o_up);
+  dio.uold = (const double*)(d + o_uo); dio.nbr_xy = (const double*)(d + o_nb); dio.pose = (const double*)(d + o_po);
+  dio.nbr_count = io->nbr_count ? (const int32_t*)(d + o_nc) : nullptr;
+  dio.z = io->z ? (double*)(d + o_z) : nullptr; dio.planes = io->planes ? (double*)(d + o_pl) : nullptr;
+  dio.y_ineq = io->y_ineq ? (double*)(d + o_yi) : nullptr; dio.y_eq = io->y_eq ? (double*)(d + o_ye) : nullptr;
+  dio.obj = io->obj ? (double*)(d + o_ob) : nullptr; dio.status = io->status ? (int32_t*)(d + o_st) : nullptr;
+  dio.iters = io->iters ? (int32_t*)(d + o_it) : nullptr; dio.pivots = io->pivots ? (int32_t*)(d + o_pv) : nullptr;
+  const int rc = dmpc_solve_batch(h, &dio, (void*)s);
+  if (rc) return rc;
+  D2H(io->z, o_z, (size_t)B * n * 8); D2H(io->planes, o_pl, (size_t)B * N * 3 * nn * 8); D2H(io->y_ineq, o_yi, (size_t)B * mi * 8);
+  D2H(io->y_eq, o_ye, (size_t)B * me * 8); D2H(io->obj, o_ob, (size_t)B * 8); D2H(io->status, o_st, (size_t)B * 4);
+  D2H(io->iters, o_it, (size_t)B * 4); D2H(io->pivots, o_pv, (size_t)B * 4);
+#undef H2D
+#undef D2H
+  CUDA_TRY(h, cudaStreamSynchronize(s));
+  return DMPC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// DMPC bookkeeping kernels (planner/scripts/LPV_HP_N_main.py:106,113-117; LPV_Planner.py:179-180).
+__global__ void shift_pack_kernel(int B, int N, const double* __restrict__ z, double* __restrict__ x0, double* __restrict__ xprev,
+                                  double* __restrict__ uprev, double* __restrict__ uold, double* __restrict__ xy) {
+  const int n = 16 * N + 12;
+  const long long total = (long long)B * n;
+  for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
+    const int b = (int)(w / n), j = (int)(w % n);
+    const double v = z[w];
+    if (j < 12 * (N + 1)) {
+      const int t = j / 12, r = j % 12;
+      if (r >= 9) continue;
+      if (t == 1 && x0) x0[(size_t)b * 9 + r] = v;                                  // r.x0 = x_pred[i][1,:]
+      if (t >= 1 && xprev) xprev[((size_t)b * N + (t - 1)) * 9 + r] = v;            // x_old = x_pred[1:,:]
+      if (r >= 7 && xy) xy[((size_t)b * (N + 1) + t) * 2 + (r - 7)] = v;            // agents[t,i,:] = xPred[t,7:9]
+    } else if (j < 12 * (N + 1) + 2 * N) {
+      const int q = j - 12 * (N + 1);
+      if (uprev) uprev[(size_t)b * 2 * N + q] = v;                                  // u_old = u_pred (not shifted)
+      if (q < 2 && uold) uold[(size_t)b * 2 + q] = v;                               // OldSteering / OldAccelera
+    }
+  }
+}
+
+extern "C" int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, double* d_x0, double* d_xprev, double* d_uprev,
+                               double* d_uold, double* d_xy_send, void* stream) {
+  if (!h || !d_z || B < 0) return DMPC_ERR_ARG;
+  if (B == 0) return DMPC_OK;
+  const long long total = (long long)B * (16 * h->P.N + 12);
+  const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  shift_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(B, h->P.N, d_z, d_x0, d_xprev, d_uprev, d_uold, d_xy_send);
+  h->launches++;
+  CUDA_TRY(h, cudaGetLastError());
+  return DMPC_OK;
+}
+
+__global__ void gather_neighbours_kernel(int S, int A_total, int A_local, int agent_offset, int T, int nn,
+                                         const double* __restrict__ xy_all, const int* __restrict__ nbr_idx,
+                                         double* __restrict__ nbr_xy, double* __restrict__ pose) {
+  const long long per = (long long)T * (nn + 1);
+  const long long total = (long long)S * A_local * per;
+  for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
+    const int b = (int)(w / per);
+    const int rem = (int)(w % per), t = rem / (nn + 1), j = rem % (nn + 1);
+    const int s = b / A_local, al = b % A_local, ag = agent_offset + al;
+    if (j == nn) {
+      const double* src = xy_all + (((size_t)s * A_total + ag) * T + t) * 2;
+      pose[((size_t)b * T + t) * 2] = src[0]; pose[((size_t)b * T + t) * 2 + 1] = src[1];
+    } else {
+      const int k = nbr_idx[(size_t)b * nn + j];
+      double vx, vy;
+      if (k >= 0) { const double* src = xy_all + (((size_t)s * A_total + k) * T + t) * 2; vx = src[0]; vy = src[1]; }
+      else { const double* src = xy_all + (((size_t)s * A_total + ag) * T + t) * 2; vx = src[0] + 1e3; vy = src[1] + 1e3; }
+      double* dst = nbr_xy + (((size_t)b * T + t) * nn + j) * 2;
+      dst[0] = vx; dst[1] = vy;
+    }
+  }
+}
+
+extern "C" int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
+                                      const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
+                                      void* stream) {
+  if (!h || !d_xy_all || !d_pose || S < 0 || A_local < 0 || A_total < A_local) return DMPC_ERR_ARG;
+  if (S == 0 || A_local == 0) return DMPC_OK;
+  const int T = h->P.N + 1, nn = h->P.nn;
+  if (nn > 0 && (!d_nbr_idx || !d_nbr_xy)) return DMPC_ERR_ARG;
+  const long long total = (long long)S * A_local * T * (nn + 1);
+  const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  gather_neighbours_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(S, A_total, A_local, agent_offset, T, nn, d_xy_all,
+                                                                     d_nbr_idx, d_nbr_xy, d_pose);
+  h->launches++;
+  CUDA_TRY(h, cudaGetLastError());
+  return DMPC_OK;
+}

@@ -47,18 +47,18 @@ typedef struct dmpc_params {
   double seg_hw[DMPC_MAX_SEG];   /* halfWidth[:]                                             */
 } dmpc_params;
 
-/* Solver options.  Defaults (dmpc_default_options) follow what osqp_solve_qp passes
- * (LPV_Planner.py:233: polish=True, max_iter=500000) and OSQP's documented defaults. */
+/* Solver options.  The reference calls OSQP with polish=True, max_iter=500000 (LPV_Planner.py:233); the B200 path
+ * returns the KKT-certified optimum of the same QP (OSQP's limit as eps -> 0, i.e. a successful polish), found by
+ * active-set polish rounds with an interior-point phase as globalisation. */
 typedef struct dmpc_options {
-  double rho;             /* 0.1                                                             */
-  double sigma;           /* 1e-6                                                            */
-  double alpha;           /* 1.6                                                             */
-  double eps_abs, eps_rel;/* ADMM stopping tolerance before polish (1e-3, 1e-3)              */
-  int32_t max_iter;       /* total ADMM iterations per QP before status -2                    */
-  int32_t check_every;    /* termination / adaptive-rho period (25)                          */
-  int32_t polish;         /* 1: active-set polish + KKT certificate (exact optimum)          */
-  int32_t polish_max_pivots; /* active-set correction rounds per polish attempt              */
-  double cert_tol;        /* KKT certificate tolerance (relative), 1e-9                      */
+  double polish_delta;    /* regularisation of the polish KKT solve (OSQP's `delta`), 1e-9            */
+  double cert_tol;        /* relative KKT certificate tolerance, 1e-9                                  */
+  double ipm_mu0;         /* first complementarity target of the interior-point phase, 1e-6            */
+  int32_t polish_refine;  /* refinement steps per polish solve (OSQP's polish_refine_iter), 4         */
+  int32_t pdas_first;     /* active-set polish rounds tried before the interior-point phase, 6         */
+  int32_t pdas_after;     /* active-set polish rounds after each interior-point phase, 4               */
+  int32_t ipm_max_iter;   /* interior-point iteration cap per phase, 60                                */
+  int32_t reserved0, reserved1;
 } dmpc_options;
 
 /* Per-QP status values mirror OSQP's status_val so `feasible` is derived as LPV_Planner.py:246-248. */
