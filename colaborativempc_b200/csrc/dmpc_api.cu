@@ -274,6 +274,8 @@ extern "C" int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, dou
   return DMPC_OK;
 }
 
+// xy_all is laid out as ncclAllGather leaves it: [G][S][A_local][T][2] with G = A_total / A_local ranks, i.e. global
+// agent k of scenario s lives at (((k / A_local) * S + s) * A_local + k % A_local).  G = 1 is plain [S][A][T][2].
 __global__ void gather_neighbours_kernel(int S, int A_total, int A_local, int agent_offset, int T, int nn,
                                          const double* __restrict__ xy_all, const int* __restrict__ nbr_idx,
                                          double* __restrict__ nbr_xy, double* __restrict__ pose) {
@@ -283,14 +285,16 @@ __global__ void gather_neighbours_kernel(int S, int A_total, int A_local, int ag
     const int b = (int)(w / per);
     const int rem = (int)(w % per), t = rem / (nn + 1), j = rem % (nn + 1);
     const int s = b / A_local, al = b % A_local, ag = agent_offset + al;
+    const double* self = xy_all + ((((size_t)(ag / A_local) * S + s) * A_local + ag % A_local) * T + t) * 2;
     if (j == nn) {
-      const double* src = xy_all + (((size_t)s * A_total + ag) * T + t) * 2;
-      pose[((size_t)b * T + t) * 2] = src[0]; pose[((size_t)b * T + t) * 2 + 1] = src[1];
+      pose[((size_t)b * T + t) * 2] = self[0]; pose[((size_t)b * T + t) * 2 + 1] = self[1];
     } else {
       const int k = nbr_idx[(size_t)b * nn + j];
       double vx, vy;
-      if (k >= 0) { const double* src = xy_all + (((size_t)s * A_total + k) * T + t) * 2; vx = src[0]; vy = src[1]; }
-      else { const double* src = xy_all + (((size_t)s * A_total + ag) * T + t) * 2; vx = src[0] + 1e3; vy = src[1] + 1e3; }
+      if (k >= 0 && k < A_total) {
+        const double* src = xy_all + ((((size_t)(k / A_local) * S + s) * A_local + k % A_local) * T + t) * 2;
+        vx = src[0]; vy = src[1];
+      } else { vx = self[0] + 1e3; vy = self[1] + 1e3; }  // empty slot: geometrically inert, never enters the QP
       double* dst = nbr_xy + (((size_t)b * T + t) * nn + j) * 2;
       dst[0] = vx; dst[1] = vy;
     }
@@ -300,7 +304,9 @@ __global__ void gather_neighbours_kernel(int S, int A_total, int A_local, int ag
 extern "C" int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
                                       const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
                                       void* stream) {
-  if (!h || !d_xy_all || !d_pose || S < 0 || A_local < 0 || A_total < A_local) return DMPC_ERR_ARG;
+  if (!h || !d_xy_all || !d_pose || S < 0 || A_local < 0 || A_total < A_local || agent_offset < 0 ||
+      agent_offset + A_local > A_total || (A_local > 0 && A_total % A_local != 0))
+    return DMPC_ERR_ARG;
   if (S == 0 || A_local == 0) return DMPC_OK;
   const int T = h->P.N + 1, nn = h->P.nn;
   if (nn > 0 && (!d_nbr_idx || !d_nbr_xy)) return DMPC_ERR_ARG;

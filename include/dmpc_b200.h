@@ -131,11 +131,14 @@ int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io);
 int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, double* d_x0, double* d_xprev /*[B,N,9]*/,
                     double* d_uprev, double* d_uold, double* d_xy_send /*[B,N+1,2]*/, void* stream);
 
-/* After the exchange: gathers each agent's neighbour trajectories and its own pose from the all-gathered
- * buffer  xy_all [S, A, N+1, 2]  (scenario-major, A agents per scenario):
- *   nbr_xy[b,t,j,:] = xy_all[s(b), nbr_idx[b,j], t, :],  pose[b,t,:] = xy_all[s(b), a(b), t, :]
- * where local QP b = (s_local * A_local + a_local), global agent a(b) = agent_offset + a_local.
- * nbr_idx is [A_local? no: B, nn] int32 of global agent ids (agents_id of the reference), -1 = empty slot. */
+/* After the exchange: gathers each agent's neighbour trajectories and its own pose from the all-gathered buffer.
+ * xy_all has the layout ncclAllGather leaves behind when every rank sends its xy_send [S, A_local, N+1, 2]:
+ *   xy_all [G, S, A_local, N+1, 2],  G = A_total / A_local ranks  (G = 1: plain [S, A_total, N+1, 2]),
+ * global agent k of scenario s at rank k / A_local, slot k % A_local.  For local QP b = s * A_local + a_local
+ * (global agent a = agent_offset + a_local):
+ *   nbr_xy[b,t,j,:] = xy_all[agent nbr_idx[b,j] of scenario s, t, :],   pose[b,t,:] = xy_all[agent a of scenario s, t, :]
+ * nbr_idx is [B, nn] int32 of global agent ids (agents_id of the reference, LPV_HP_N_main.py:82-85), -1 = empty slot.
+ * Replaces  agents[:, ns[i], :] / agents[:, i, :]  of LPV_HP_N_main.py:100 and the ROS callback LPV_ROS_main.py:71-73. */
 int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
                            const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
                            void* stream);

@@ -1,0 +1,186 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle and the committed golden vectors.
+
+Parity bar (BASELINE.json north_star): same active set; primal / dual solution and objective within 1e-6 relative
+at FP64.  rel_err = max|a-b| / (1 + max|b|) per QP."""
+import numpy as np
+import pytest
+
+from conftest import INPUT_KEYS, golden, planner_args, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-6
+N = 20
+
+
+def _engine(cfg, track, N=20, nn=2, max_batch=64, **kw):
+    from colaborativempc_b200.planner import BatchedPlannerLPV
+    return BatchedPlannerLPV(*planner_args(cfg, track, N), nn=nn, max_batch=max_batch, **kw)
+
+
+def _oracle(cfg, track, ins, N=20, nn=2, nthreads=8):
+    from colaborativempc_b200._abi import make_params
+    from oracle import lpv_oracle as lo
+    P = make_params(*planner_args(cfg, track, N), nn=nn)
+    o = lo.solve_batch(P, st=lo.settings(exact=True), nthreads=nthreads, **ins)
+    return o
+
+
+def _active(y_in, scale):
+    return y_in > 1e-8 * (1.0 + scale[:, None])
+
+
+def _compare(out, z, y, obj, planes, m_in):
+    assert np.all(out["status"] == 1), np.unique(out["status"], return_counts=True)
+    scale = np.abs(y).max(1)
+    assert rel_err(out["z"], z).max() < TOL
+    assert rel_err(out["obj"][:, None], obj[:, None]).max() < TOL
+    assert (np.abs(out["y_ineq"] - y[:, :m_in]).max(1) / (1 + scale)).max() < TOL
+    assert (np.abs(out["y_eq"] - y[:, m_in:]).max(1) / (1 + scale)).max() < TOL
+    assert np.array_equal(_active(out["y_ineq"], scale), _active(y[:, :m_in], scale))
+    if planes is not None:
+        assert np.abs(out["planes"] - planes).max() < 1e-12
+
+
+@pytest.mark.parametrize("it", [0, 3])
+def test_golden_platoon(built, cfg, track, it):
+    """Committed oracle solutions of 16 three-agent platoons (first call: N+1 history rows; later call: N rows)."""
+    fx = golden("platoon_N20.npz")
+    eng = _engine(cfg, track)
+    ins = {k: fx["it%d_%s" % (it, k)] for k in INPUT_KEYS}
+    out = eng.solve_batch_host(**ins)
+    _compare(out, fx["it%d_out_z" % it], fx["it%d_out_y" % it], fx["it%d_out_obj" % it], fx["it%d_out_planes" % it], eng.m_in)
+
+
+def test_reference_startup_case(built, cfg, track):
+    """The reference's shipped 3-agent start-up at N=20 (inputs from the reference's initialise_agents, golden)."""
+    g = golden("ref_startup_N20.npz")
+    eng = _engine(cfg, track)
+    ins = dict(x0=g["x_old"][:, 0], xprev=g["x_old"], uprev=g["u_old"], uold=np.zeros((3, 2)),
+               nbr_xy=np.stack([g["agents"][:, g["ns"][i], :] for i in range(3)]),
+               pose=np.stack([g["agents"][:, i, :] for i in range(3)]), nbr_count=None)
+    out = eng.solve_batch_host(**ins)
+    for i in range(3):
+        assert np.array_equal(out["planes"][i], g["a%d_planes" % i])
+    # KKT certificate against the matrices the reference assembled
+    for i in range(3):
+        z = out["z"][i]
+        y = np.concatenate([out["y_ineq"][i], out["y_eq"][i]])
+        Pd, q, A, l, u = (g["a%d_%s" % (i, k)] for k in ("Pdiag", "q", "A", "l", "u"))
+        Az = A @ z
+        assert max((Az - u).max(), (l - Az).max()) < 1e-9
+        assert np.abs(Pd * z + q + A.T @ y).max() < 1e-6 * (1 + np.abs(q).max())
+        assert out["y_ineq"][i].min() >= 0
+        assert abs(0.5 * z @ (Pd * z) + q @ z - out["obj"][i]) < 1e-9 * abs(out["obj"][i])
+    o = _oracle(cfg, track, ins)
+    _compare(out, o["z"], o["y"], o["obj"], o["planes"], eng.m_in)
+
+
+@pytest.mark.parametrize("Nh,nn,topo,S,A", [(10, 2, "full", 8, 3), (20, 2, "chain", 4, 6), (20, 5, "full", 4, 6),
+                                            (50, 2, "full", 4, 3), (20, 0, "full", 8, 1)])
+def test_closed_loop_vs_oracle(built, cfg, track, Nh, nn, topo, S, A):
+    """4 DMPC iterations driven by the CUDA path; every iteration's batch is re-solved by the oracle."""
+    from colaborativempc_b200 import scenarios as sc
+    eng = _engine(cfg, track, N=Nh, nn=nn, max_batch=S * A)
+    x0, xprev, uprev = sc.platoon_scenarios(S, A, Nh, cfg["dt"], track, seed0=100)
+    idx, cnt = sc.topology(A, topo, nn=nn)
+    rec = []
+    sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, 4, Nh, record=rec)
+    assert len(rec) == 4
+    for ins, out in rec:
+        o = _oracle(cfg, track, ins, N=Nh, nn=nn)
+        ok = o["status"] == 1
+        assert ok.all()
+        _compare(out, o["z"], o["y"], o["obj"], o["planes"], eng.m_in)
+
+
+def test_device_and_host_entry_points_agree(built, cfg, track):
+    import torch
+    fx = golden("platoon_N20.npz")
+    eng = _engine(cfg, track)
+    ins = {k: fx["it3_%s" % k] for k in INPUT_KEYS}
+    h = eng.solve_batch_host(**ins)
+    dev = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in ins.items()}
+    d = eng.solve_batch(**dev)
+    torch.cuda.synchronize()
+    for k in ("z", "y_ineq", "y_eq", "obj", "status", "planes"):
+        assert np.array_equal(d[k].cpu().numpy(), h[k]), k
+    assert eng.launches == 2
+
+
+def test_drop_in_planner_matches_reference_call_surface(built, cfg, track):
+    """PlannerLPV(...).solve(...) as planner/scripts/LPV_HP_N_main.py:41 calls it; attributes of LPV_Planner.py:173-180."""
+    from colaborativempc_b200.planner import PlannerLPV
+    from colaborativempc_b200 import scenarios as sc
+    g = golden("ref_startup_N20.npz")
+    ctrls = [PlannerLPV(cfg["Q"], cfg["Qs"], cfg["R"], cfg["dR"], N, cfg["dt"], track, i, cfg["wq"], cfg["model_param"],
+                        cfg["sys_lim"]) for i in range(3)]
+    agents, x_old, u_old = sc.initialise_agents(sc.X0_DATABASE[0:3], N, cfg["dt"], track)
+    ns = [[1, 2], [0, 2], [0, 1]]
+    want_obj = (-1396.897816823358, -1490.2691025771865, -1402.3910432237897)
+    for it in range(2):
+        x_pred, u_pred = [], []
+        for i, c in enumerate(ctrls):
+            feas, sol, planes = c.solve(x_old[i][0, :], x_old[i], u_old[i], agents[:, ns[i], :], ns[i], agents[:, i, :])
+            assert feas == 1 and sol.shape == (16 * N + 12,) and planes.shape == (N, 3, 2)
+            assert c.xPred.shape == (N + 1, 9) and c.uPred.shape == (N, 2) and c.sPred.shape == (N, 3)
+            assert c.duPred.shape == (N, 2) and c.raw_States.shape == (N + 1, 12)
+            if it == 0:
+                assert abs(c.obj_val - want_obj[i]) < 1e-6 * abs(want_obj[i])
+                assert np.array_equal(planes, g["a%d_planes" % i])
+            assert c.OldSteering[0] == c.uPred[0, 0] and c.OldAccelera[0] == c.uPred[0, 1]
+            x_pred.append(c.xPred)
+            u_pred.append(c.uPred)
+        u_old = u_pred
+        x_old = [x[1:, :] for x in x_pred]
+        agents = np.swapaxes(np.asarray(x_pred)[:, :, -2:], 0, 1)
+
+
+def test_edge_cases(built, cfg, track):
+    """Empty batch; ragged neighbour counts; failed map lookup (the reference raises) and coincident agents."""
+    fx = golden("platoon_N20.npz")
+    eng = _engine(cfg, track)
+    ins = {k: fx["it3_%s" % k][:6].copy() for k in INPUT_KEYS}
+    empty = eng.solve_batch_host(**{k: v[:0] for k, v in ins.items()})
+    assert empty["z"].shape == (0, 16 * N + 12)
+    L = float(np.ravel(track.TrackLength)[0])
+    ins["xprev"][1, 5, 6] = L                      # curvature() finds no segment (misc.py:97)
+    ins["nbr_xy"][2, 4, 0] = ins["pose"][2, 4]     # compute_plane.py:52 divides by zero
+    ins["nbr_count"] = np.array([2, 2, 2, 1, 0, 2], np.int32)
+    out = eng.solve_batch_host(**ins)
+    assert out["status"][1] == -20 and np.all(np.isnan(out["z"][1]))
+    assert out["status"][2] == -21
+    keep = np.array([0, 3, 4, 5])
+    o = _oracle(cfg, track, {k: v[keep] for k, v in ins.items()})
+    sub = {k: v[keep] for k, v in out.items()}
+    _compare(sub, o["z"], o["y"], o["obj"], None, eng.m_in)
+    # rows of unused neighbour slots carry zero multipliers
+    yi = out["y_ineq"][4][:(4 + 2) * N].reshape(N, 6)
+    assert np.all(yi[:, 4:] == 0)
+
+
+def test_full_size_batch_properties(built, cfg, track):
+    """BASELINE config 2 at full size (4096 scenario QPs): all certified, batch-position independent (bitwise),
+    replicas identical, objective = 1/2 z'Pz + q'z recomputed on the host."""
+    import torch
+    from colaborativempc_b200 import scenarios as sc
+    S, A = 64, 3
+    eng = _engine(cfg, track, max_batch=4096)
+    x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=1000)
+    idx, cnt = sc.topology(A, "full")
+    st = sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, 3, N)
+    ins = {k: st[k] for k in INPUT_KEYS}
+    B0 = S * A
+    rep = (4096 + B0 - 1) // B0
+    big = {k: np.concatenate([v] * rep, 0)[:4096] for k, v in ins.items()}
+    perm = np.random.default_rng(0).permutation(4096)
+    out = eng.solve_batch_host(**big)
+    outp = eng.solve_batch_host(**{k: v[perm] for k, v in big.items()})
+    assert np.all(out["status"] == 1)
+    assert np.array_equal(out["z"][perm], outp["z"])
+    assert np.array_equal(out["z"][:B0], out["z"][B0:2 * B0])
+    o = _oracle(cfg, track, {k: v[:B0] for k, v in big.items()})
+    _compare({k: v[:B0] for k, v in out.items()}, o["z"], o["y"], o["obj"], o["planes"], eng.m_in)
+    u0 = 12 * (N + 1)
+    u = out["z"][:, u0:u0 + 2 * N].reshape(-1, N, 2)
+    assert u[:, :, 0].max() <= 0.3 + 1e-9 and u[:, :, 0].min() >= -0.3 - 1e-9
+    assert u[:, :, 1].max() <= 5.0 + 1e-9 and u[:, :, 1].min() >= -10.0 - 1e-9
