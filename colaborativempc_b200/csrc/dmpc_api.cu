@@ -7,12 +7,14 @@
 #include <new>
 
 #include "qp_kernel.cuh"
+#include "qp2_kernel.cuh"
 
 struct dmpc_handle {
   dmpc_params params;
   dmpc_options opt;
   DevParams P;
   int device, max_batch, smem_limit;
+  int fast;  // 1: lpv_qp_fast_kernel (qp2_*.cuh), 0: lpv_qp_solve_kernel (generic)
   size_t smem_bytes;
   long long gws_stride;
   double* d_gws;
@@ -39,7 +41,7 @@ extern "C" void dmpc_default_options(dmpc_options* o) {
   if (!o) return;
   o->polish_delta = 1e-9; o->cert_tol = 1e-9; o->ipm_mu0 = 1e-6;
   o->polish_refine = 4; o->pdas_first = 6; o->pdas_after = 4; o->ipm_max_iter = 60;
-  o->reserved0 = o->reserved1 = 0;
+  o->engine = DMPC_ENGINE_AUTO; o->reserved1 = 0;
 }
 
 static void apply_options(dmpc_handle* h) {
@@ -50,7 +52,8 @@ static void apply_options(dmpc_handle* h) {
 
 static bool options_ok(const dmpc_options* o) {
   return o->polish_delta > 0 && o->polish_delta < 1e-3 && o->cert_tol > 0 && o->ipm_mu0 > 0 && o->polish_refine >= 0 &&
-         o->polish_refine <= 32 && o->pdas_first >= 0 && o->pdas_after >= 1 && o->ipm_max_iter >= 1;
+         o->polish_refine <= 32 && o->pdas_first >= 0 && o->pdas_after >= 1 && o->ipm_max_iter >= 1 && o->engine >= 0 &&
+         o->engine <= 2;
 }
 
 // symmetric matrix as OSQP sees it: the upper triangle of the user's array (LPV_Planner.py:156 hands csr(M), and
@@ -137,6 +140,18 @@ extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_
   int optin = 0;
   CUDA_TRY(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
   h->smem_limit = optin;
+  {  // fast engine: the whole packed workspace in shared memory (qp2_engine.cuh)
+    Ctx2 c2;
+    const size_t sb2 = carve_workspace2(c2, nullptr, P.N, P.nn, P.nrows) + 16;
+    const bool fits = sb2 + 1024 <= (size_t)optin && 2 * P.N <= 255 && P.N <= 4095;
+    if (h->opt.engine == DMPC_ENGINE_FAST && !fits)
+      return fail(h, DMPC_ERR_UNSUPPORTED, "horizon too long for the fast engine%s");
+    if (fits && h->opt.engine != DMPC_ENGINE_GENERIC) {
+      h->fast = 1; h->smem_bytes = sb2; h->gws_stride = 0;
+      CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb2));
+      return DMPC_OK;
+    }
+  }
   Ctx c;
   bool placed = false;
   for (int mode = 0; mode < 3 && !placed; ++mode) {
@@ -163,6 +178,7 @@ extern "C" const char* dmpc_last_error(const dmpc_handle* h) { return h ? h->err
 extern "C" int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt) {
   if (!h || !opt) return DMPC_ERR_ARG;
   if (!options_ok(opt)) return fail(h, DMPC_ERR_ARG, "bad options%s");
+  if (opt->engine != h->opt.engine) return fail(h, DMPC_ERR_ARG, "the engine is chosen at dmpc_create%s");
   h->opt = *opt;
   apply_options(h);
   return DMPC_OK;
@@ -184,7 +200,8 @@ extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* s
   bp.z = io->z; bp.planes = io->planes; bp.y_ineq = io->y_ineq; bp.y_eq = io->y_eq; bp.obj = io->obj;
   bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
   bp.gws = h->d_gws; bp.gws_stride = h->gws_stride;
-  lpv_qp_solve_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+  if (h->fast) lpv_qp_fast_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+  else lpv_qp_solve_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
   h->launches++;
   CUDA_TRY(h, cudaGetLastError());
   return DMPC_OK;

@@ -9,7 +9,8 @@
 
 // planes (N,3,nn) + distance weights folded into the linear cost of x,y (LPV_Planner.py:416-422).
 // Returns nonzero if ego and a neighbour coincide (compute_plane.py:52 divides by zero there).
-__device__ __forceinline__ int setup_planes(const Ctx& c, const DevParams& P, const double* nbr, const double* pose,
+template <class CT>
+__device__ __forceinline__ int setup_planes(const CT& c, const DevParams& P, const double* nbr, const double* pose,
                                             double* planes_out) {
   int bad = 0;
   for (int h = threadIdx.x; h < c.N; h += QP_THREADS) {
@@ -44,7 +45,8 @@ __device__ __forceinline__ int setup_planes(const Ctx& c, const DevParams& P, co
 
 // A_k = I + dt*Ac, B_k = dt*Bc along the previous prediction (LPV_Planner.py:491-589).  Only the first three
 // columns of Ac are non-zero, so A_k is stored as its 9x3 column block.  Returns nonzero on a failed map lookup.
-__device__ __forceinline__ int setup_linearise(const Ctx& c, const DevParams& P, const double* xprev, int rows,
+template <class CT>
+__device__ __forceinline__ int setup_linearise(const CT& c, const DevParams& P, const double* xprev, int rows,
                                                const double* uprev) {
   int bad = 0;
   for (int k = threadIdx.x; k < max(c.N, rows); k += QP_THREADS) {

@@ -58,7 +58,9 @@ typedef struct dmpc_options {
   int32_t pdas_first;     /* active-set polish rounds tried before the interior-point phase, 6         */
   int32_t pdas_after;     /* active-set polish rounds after each interior-point phase, 4               */
   int32_t ipm_max_iter;   /* interior-point iteration cap per phase, 60                                */
-  int32_t reserved0, reserved1;
+  int32_t engine;         /* 0 auto, 1 generic engine (any horizon, global spill), 2 fast engine (workspace packed in
+                             shared memory; dmpc_create fails if the horizon does not fit)                     */
+  int32_t reserved1;
 } dmpc_options;
 
 /* Per-QP status values mirror OSQP's status_val so `feasible` is derived as LPV_Planner.py:246-248. */
@@ -72,6 +74,8 @@ enum dmpc_status {
   DMPC_DEGENERATE_PLANE = -21,  /* ego and neighbour coincide: compute_plane.py:52 divides by zero        */
   DMPC_UNSOLVED = -10
 };
+
+enum dmpc_engine { DMPC_ENGINE_AUTO = 0, DMPC_ENGINE_GENERIC = 1, DMPC_ENGINE_FAST = 2 };
 
 enum dmpc_error {
   DMPC_OK = 0,

@@ -15,13 +15,14 @@ from colaborativempc_b200.planner import BatchedPlannerLPV  # noqa: E402
 from colaborativempc_b200.track import TrackMap  # noqa: E402
 
 
-def main():
+def main(engine=0):
     N = 20
+    print("==== engine", engine)
     cfg = sc.shipped_config()
     tr = TrackMap("Highway")
     fx = np.load(os.path.join(ROOT, "tests", "golden", "platoon_N20.npz"))
     eng = BatchedPlannerLPV(cfg["Q"], cfg["Qs"], cfg["R"], cfg["dR"], N, cfg["dt"], tr, cfg["wq"], cfg["model_param"],
-                            cfg["sys_lim"], nn=2, max_batch=4096)
+                            cfg["sys_lim"], nn=2, max_batch=4096, options={"engine": engine})
     for it in (0, 3):
         ins = {k: fx["it%d_%s" % (it, k)] for k in ("x0", "xprev", "uprev", "uold", "nbr_xy", "pose", "nbr_count")}
         out = eng.solve_batch_host(**ins)
@@ -70,4 +71,5 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    for e in ([int(a) for a in sys.argv[1:]] or [2, 1]):
+        main(e)

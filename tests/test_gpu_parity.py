@@ -41,11 +41,13 @@ def _compare(out, z, y, obj, planes, m_in):
         assert np.abs(out["planes"] - planes).max() < 1e-12
 
 
+@pytest.mark.parametrize("engine", [2, 1])
 @pytest.mark.parametrize("it", [0, 3])
-def test_golden_platoon(built, cfg, track, it):
-    """Committed oracle solutions of 16 three-agent platoons (first call: N+1 history rows; later call: N rows)."""
+def test_golden_platoon(built, cfg, track, it, engine):
+    """Committed oracle solutions of 16 three-agent platoons (first call: N+1 history rows; later call: N rows),
+    on the fast (shared-memory packed) and on the generic engine."""
     fx = golden("platoon_N20.npz")
-    eng = _engine(cfg, track)
+    eng = _engine(cfg, track, options={"engine": engine})
     ins = {k: fx["it%d_%s" % (it, k)] for k in INPUT_KEYS}
     out = eng.solve_batch_host(**ins)
     _compare(out, fx["it%d_out_z" % it], fx["it%d_out_y" % it], fx["it%d_out_obj" % it], fx["it%d_out_planes" % it], eng.m_in)
