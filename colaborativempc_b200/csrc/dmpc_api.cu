@@ -142,7 +142,7 @@ extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_
   h->smem_limit = optin;
   {  // fast engine: the whole packed workspace in shared memory (qp2_engine.cuh)
     Ctx2 c2;
-    const size_t sb2 = carve_workspace2(c2, nullptr, P.N, P.nn, P.nrows) + 16;
+    const size_t sb2 = FAST_HDR_BYTES + carve_workspace2(c2, nullptr, P.N, P.nn, P.nrows);
     const bool fits = sb2 + 1024 <= (size_t)optin && 2 * P.N <= 255 && P.N <= 4095;
     if (h->opt.engine == DMPC_ENGINE_FAST && !fits)
       return fail(h, DMPC_ERR_UNSUPPORTED, "horizon too long for the fast engine%s");

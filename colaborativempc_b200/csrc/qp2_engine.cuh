@@ -18,8 +18,23 @@
 #define TRI(i) ((((i) + 1) * (i)) >> 1)
 #define ZCAP 3  // stages per Z chunk (Z aliases the linearisation block, 31N doubles >= 3 * 8N)
 
+// Solver header at the start of dynamic shared memory: what the non-inlined primitives need to rebuild their view of
+// the workspace (they take no pointer arguments, so every access stays a shared-memory access) plus the few solver
+// options and the slack weights.
+struct Hdr2 {
+  int N, nn, NR, cnt;
+  int refine, pdas_first, pdas_after, ipm_max;
+  int n_rounds, n_ipm, pad0, pad1;
+  double delta, cert_tol, ipm_mu0;
+  double Qs[9];
+};
+
+extern __shared__ __align__(16) char smem_fast[];
+
 struct Ctx2 {
   int N, nn, cnt, nu, NR, rst, Rs, RT, ntri;
+  const Hdr2* hd;
+  double* bv;  // right-hand side b of every row (LPV_Planner.py:304-369)
   // problem data
   double *Gb, *Gx, *H, *K;
   double *Acol, *Bcol, *Z;  // Z aliases Acol/Bcol (re-linearised before the outputs are written)
@@ -59,10 +74,11 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   c.cr = take((size_t)N * NR); c.g = take(c.nu);
   c.u = take(c.nu); c.rhs = take(c.nu); c.du = take(c.nu); c.tv = take(c.nu); c.rdu = take(c.nu);
   c.yt = c.tv;  // H u is consumed before any triangular solve starts
-  c.lam = take(c.RT); c.tt = take(c.RT); c.D = take(c.RT); c.res = take(c.RT);
-  c.om = take(c.RT); c.dlam = take(c.RT); c.dtt = take(c.RT);  // contiguous: set-up scratch ql (N x NR <= 2 RT)
+  c.lam = take(c.RT); c.tt = take(c.RT); c.D = take(c.RT); c.res = take(c.RT); c.bv = take(c.RT);
+  c.om = take(c.RT); c.dlam = take(c.RT); c.dtt = take(c.RT);  // contiguous: set-up scratch ql (N x NR <= 2 RT), Weff
   c.sig = take(3 * N); c.dsig = take(3 * N); c.rsig = take(3 * N); c.rds = take(3 * N);
-  c.Weff = take(10 * N); c.Si = take(6 * N); c.bh = take(4 * N); c.wo = take(4 * N); c.dob = take(4 * N);
+  c.Weff = c.om;  // 10N <= 2 RT: only alive between stage_weights2 and build_K2, when om/dlam are dead
+  c.Si = take(6 * N); c.bh = take(4 * N); c.wo = take(4 * N); c.dob = take(4 * N);
   c.rs = take(c.nu); c.lrow = take(2 * c.nu);
   c.red = take(8);
   c.hist = (unsigned long long*)take(16);
@@ -76,11 +92,23 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   return (size_t)((char*)p - sm);
 }
 
+#define FAST_HDR_BYTES ((sizeof(Hdr2) + 15) & ~(size_t)15)
+// view of this CTA's workspace, rebuilt from the header (cheap: a handful of integer multiply-adds per pointer used)
+#define CTX2_LOCAL(c)                                                            \
+  Ctx2 c;                                                                        \
+  {                                                                              \
+    const Hdr2* hd_ = (const Hdr2*)smem_fast;                                    \
+    carve_workspace2(c, smem_fast + FAST_HDR_BYTES, hd_->N, hd_->nn, hd_->NR);   \
+    c.cnt = hd_->cnt; c.hd = hd_;                                                \
+  }
+
 // index tables: tri[e] = (i << 8) | j for the packed lower triangle, rinfo[row] = (t << 4) | r for stage rows
 // (r = 15 marks an unused neighbour slot) and (k << 4) | r for box rows.
 __device__ __forceinline__ void build_tables(const Ctx2& c) {
+#pragma unroll 1
   for (int i = threadIdx.x; i < c.nu; i += QP_THREADS)
     for (int j = 0; j <= i; ++j) c.tri[TRI(i) + j] = (unsigned short)((i << 8) | j);
+#pragma unroll 1
   for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
     for (int r = 0; r < c.rst; ++r) c.rinfo[t * c.rst + r] = (unsigned short)((t << 4) | (r < 4 + c.cnt ? (r < 4 ? r : 4) : 15));
     for (int r = 0; r < 4; ++r) c.rinfo[c.Rs + 4 * t + r] = (unsigned short)((t << 4) | r);
@@ -90,7 +118,7 @@ __device__ __forceinline__ void build_tables(const Ctx2& c) {
 __device__ __forceinline__ bool row_valid2(const Ctx2& c, int j) { return j >= c.Rs || (c.rinfo[j] & 15) != 15; }
 
 // right-hand side b of row j (LPV_Planner.py:304-369 after the row re-ordering :350-362)
-__device__ __forceinline__ double row_h2(const Ctx2& c, const DevParams& P, int j) {
+__device__ __forceinline__ double row_h2_build(const Ctx2& c, const DevParams& P, int j) {
   const int ri = c.rinfo[j], r = ri & 15, t = ri >> 4;
   if (j >= c.Rs) return r == 0 ? P.max_rs : (r == 1 ? P.max_ls : (r == 2 ? P.max_ac : P.max_dc));
   if (r == 0) return -P.min_vel;
@@ -118,6 +146,7 @@ __device__ __forceinline__ double row_val2(const Ctx2& c, int j, const double* o
 
 // o[t][q] = Gb_t[q,:] . uv (+ offset): the four constrained outputs of every stage.   (syncs: caller)
 __device__ __forceinline__ void stage_outputs2(const Ctx2& c, const double* uv, double* o, bool with_offset) {
+#pragma unroll 1
   for (int w = threadIdx.x; w < 4 * c.N; w += QP_THREADS) {
     const int t = w >> 2, q = w & 3;
     const double* g = &GB(c, t, q, 0);
@@ -130,6 +159,7 @@ __device__ __forceinline__ void stage_outputs2(const Ctx2& c, const double* uv, 
 
 // A' w split into the stage-output part wo (N x 4), the slack part gs (N x 3); box part is added by apply_Gt2.
 __device__ __forceinline__ void rows_to_stage2(const Ctx2& c, const double* w, double* wo, double* gs) {
+#pragma unroll 1
   for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
     const double* wr = w + t * c.rst;
     double sx = 0.0, sy = 0.0, sw = 0.0;
@@ -149,6 +179,7 @@ __device__ __forceinline__ void rows_to_stage2(const Ctx2& c, const double* w, d
 // out[j] = base[j]*bs + ws * (sum_t Gb_t[:,j]' wo_t + box(wbox)).  `sparse`: wo is zero outside the active stages.
 __device__ __forceinline__ void apply_Gt2(const Ctx2& c, const double* wo, const double* wbox, double ws,
                                           const double* base, double bs, double* out, bool sparse) {
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) {
     double s0 = 0.0, s1 = 0.0;
     if (sparse) {
@@ -178,6 +209,7 @@ __device__ __forceinline__ void apply_Gt2(const Ctx2& c, const double* wo, const
 
 // out = H uv (H symmetric, packed lower)
 __device__ __forceinline__ void apply_H2(const Ctx2& c, const double* uv, double* out) {
+#pragma unroll 1
   for (int i = threadIdx.x; i < c.nu; i += QP_THREADS) {
     double s0 = 0.0, s1 = 0.0;
     const double* hr = c.H + TRI(i);
@@ -191,7 +223,9 @@ __device__ __forceinline__ void apply_H2(const Ctx2& c, const double* uv, double
 
 // Per-stage slack elimination for row weights D: Si = (2Qs + A_s'DA_s)^-1 (3x3), bh, Weff (4x4 symmetric), and the
 // list of stages with a non-zero row weight.  Ends with a barrier.
-__device__ __forceinline__ void stage_weights2(const Ctx2& c, const DevParams& P) {
+__device__ __forceinline__ void stage_weights2(const Ctx2& c) {
+  const double* Qs = c.hd->Qs;
+#pragma unroll 1
   for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
     const double* d = c.D + t * c.rst;
     double sxx = 0, sxy = 0, syy = 0, sx = 0, sy = 0, sd = 0;
@@ -201,8 +235,8 @@ __device__ __forceinline__ void stage_weights2(const Ctx2& c, const DevParams& P
       sx = fma(di, x, sx); sy = fma(di, y, sy); sd += di;
     }
     const double b0 = d[1], b1 = d[2] - d[3], b2 = -sx, b3 = -sy;
-    const double s00 = 2 * P.Qs[0] + d[1], s01 = 2 * P.Qs[1], s02 = 2 * P.Qs[2];
-    const double s11 = 2 * P.Qs[4] + d[2] + d[3], s12 = 2 * P.Qs[5], s22 = 2 * P.Qs[8] + sd;
+    const double s00 = 2 * Qs[0] + d[1], s01 = 2 * Qs[1], s02 = 2 * Qs[2];
+    const double s11 = 2 * Qs[4] + d[2] + d[3], s12 = 2 * Qs[5], s22 = 2 * Qs[8] + sd;
     const double c00 = s11 * s22 - s12 * s12, c01 = s02 * s12 - s01 * s22, c02 = s01 * s12 - s02 * s11;
     const double c11 = s00 * s22 - s02 * s02, c12 = s01 * s02 - s00 * s12, c22 = s00 * s11 - s01 * s01;
     const double idet = 1.0 / (s00 * c00 + s01 * c01 + s02 * c02);
@@ -235,6 +269,7 @@ __device__ __forceinline__ void stage_weights2(const Ctx2& c, const DevParams& P
 
 // ro_t = -Bh Si rsig_t (stage-output space), used to fold the slack right-hand side into the u system
 __device__ __forceinline__ void slack_rhs_to_outputs2(const Ctx2& c, const double* rsig, double* ro) {
+#pragma unroll 1
   for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
     const double* si = c.Si + 6 * t;
     const double* bh = c.bh + 4 * t;
@@ -248,6 +283,7 @@ __device__ __forceinline__ void slack_rhs_to_outputs2(const Ctx2& c, const doubl
 
 // dsig_t = Si (rsig_t - Bh' dob_t)
 __device__ __forceinline__ void slack_backsolve2(const Ctx2& c, const double* rsig, const double* dob, double* dsig) {
+#pragma unroll 1
   for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
     const double* si = c.Si + 6 * t;
     const double* bh = c.bh + 4 * t;
@@ -264,6 +300,7 @@ __device__ __forceinline__ void slack_backsolve2(const Ctx2& c, const double* rs
 // K = H + sum_{t active} Gb_t' Weff_t Gb_t + diag(box weights), packed lower.  Ends with a barrier.
 __device__ __forceinline__ void build_K2(const Ctx2& c) {
   const int nas = *c.nas;
+#pragma unroll 1
   for (int e = threadIdx.x; e < c.ntri; e += QP_THREADS) {
     const int ij = c.tri[e], i = ij >> 8, j = ij & 255;
     double s = c.H[e];
@@ -281,6 +318,7 @@ __device__ __forceinline__ void build_K2(const Ctx2& c) {
       const int t = c.asl[c0 + sc];
       const double* we = c.Weff + 10 * t;
       double* z = c.Z + (size_t)sc * 4 * c.nu;
+#pragma unroll 1
       for (int j = threadIdx.x; j < 2 * (t + 1); j += QP_THREADS) {
         const double g0 = GB(c, t, 0, j), g1 = GB(c, t, 1, j), g2 = GB(c, t, 2, j), g3 = GB(c, t, 3, j);
         z[j] = we[0] * g0 + we[1] * g1 + we[2] * g2 + we[3] * g3;
@@ -290,6 +328,7 @@ __device__ __forceinline__ void build_K2(const Ctx2& c) {
       }
     }
     __syncthreads();
+#pragma unroll 1
     for (int e = threadIdx.x; e < c.ntri; e += QP_THREADS) {
       const int ij = c.tri[e], i = ij >> 8, j = ij & 255;
       double s = c.K[e];
@@ -309,62 +348,67 @@ __device__ __forceinline__ void build_K2(const Ctx2& c) {
 }
 
 // In place: K (SPD, packed lower) -> L^-1 (packed lower), K = L L'.  One barrier per pivot.  Non-positive pivots are
-// floored (returns nonzero then).  Requires QP_THREADS = 128 (warps 0-2: trailing update, warp 3: row k of L^-1).
-__device__ __forceinline__ int chol_inverse(const Ctx2& c) {
+// floored.  The trailing triangle of step k is walked through the tri[] table (item e' -> (i', j'), shifted by k+1),
+// so every lane of the updating warps has work; the remaining warps write row k of L^-1 over row k of K.
+__device__ __forceinline__ void chol_inverse(const Ctx2& c) {
   const int n = c.nu, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int bad = 0;
   if (threadIdx.x == 0) {
     double d = c.K[0];
-    if (!(d > 1e-300)) { d = 1e-30; bad = 1; }
+    if (!(d > 1e-300)) d = 1e-30;
     c.rs[0] = rsqrt(d);
   }
   __syncthreads();
+#pragma unroll 1
   for (int k = 0; k < n; ++k) {
     const double rsk = c.rs[k];
-    if (warp < 3) {
+    const int nl = k < 14 ? 1 : (k < 27 ? 2 : 3);  // warps on the L^-1 row; the others update the trailing block
+    if (warp < QP_WARPS - nl) {
       const double invd = rsk * rsk;
-      const double* rk = c.K;  // column k entries: K[TRI(i) + k]
-      for (int j = k + 1 + warp; j < n; j += 3) {
-        const double ajk = rk[TRI(j) + k] * invd;
-        for (int i = j + lane; i < n; i += 32) {
-          const int e = TRI(i) + j;
-          const double v = fma(-rk[TRI(i) + k], ajk, c.K[e]);
-          c.K[e] = v;
-          if (i == k + 1) {  // (then j == k+1 too): next pivot
-            double d = v;
-            if (!(d > 1e-300)) { d = 1e-30; bad = 1; }
-            c.rs[k + 1] = rsqrt(d);
-          }
+      const int m = n - 1 - k, items = (m * (m + 1)) >> 1, stride = 32 * (QP_WARPS - nl);
+#pragma unroll 2
+      for (int e = threadIdx.x; e < items; e += stride) {
+        const int ij = c.tri[e], i = k + 1 + (ij >> 8), j = k + 1 + (ij & 255);
+        const int ti = TRI(i);
+        const double v = fma(-c.K[ti + k] * invd, c.K[TRI(j) + k], c.K[ti + j]);
+        c.K[ti + j] = v;
+        if (e == 0) {  // (i, j) = (k+1, k+1): next pivot
+          double d = v;
+          if (!(d > 1e-300)) d = 1e-30;
+          c.rs[k + 1] = rsqrt(d);
         }
       }
     } else {
+      const int lw = warp - (QP_WARPS - nl);  // 0 .. nl-1
       // stage row k+1 of L (scaled) for the next step; all of its entries are final already
-      if (k + 1 < n) {
+      if (lw == 0 && k + 1 < n) {
         double* ln = c.lrow + ((k + 1) & 1) * n;
         const double* row = c.K + TRI(k + 1);
         for (int j = lane; j <= k; j += 32) ln[j] = row[j] * c.rs[j];
       }
       // row k of L^-1:  Linv[k][t] = -(sum_{j=t}^{k-1} L[k][j] Linv[j][t]) / L[k][k]
       const double* lk = c.lrow + (k & 1) * n;
-      for (int t = lane; t <= k; t += 32) {
+      for (int t = lane + 32 * lw; t <= k; t += 32 * nl) {
         double s0 = 0.0, s1 = 0.0;
-        int j = t;
+        int j = t, tj = TRI(t) + t;
+#pragma unroll 1
         for (; j + 1 < k; j += 2) {
-          s0 = fma(lk[j], c.K[TRI(j) + t], s0);
-          s1 = fma(lk[j + 1], c.K[TRI(j + 1) + t], s1);
+          s0 = fma(lk[j], c.K[tj], s0);
+          tj += j + 1;
+          s1 = fma(lk[j + 1], c.K[tj], s1);
+          tj += j + 2;
         }
-        for (; j < k; ++j) s0 = fma(lk[j], c.K[TRI(j) + t], s0);
+        if (j < k) s0 = fma(lk[j], c.K[tj], s0);
         c.K[TRI(k) + t] = (t == k) ? rsk : -(s0 + s1) * rsk;
       }
     }
     __syncthreads();
   }
-  return bad;
 }
 
 // x <- K^-1 x with K^-1 = Linv' Linv (Linv packed lower in c.K).  Ends with a barrier.
 __device__ __forceinline__ void chol_solve2(const Ctx2& c, double* x) {
   const int n = c.nu;
+#pragma unroll 1
   for (int i = threadIdx.x; i < n; i += QP_THREADS) {
     const double* r = c.K + TRI(i);
     double s0 = 0.0, s1 = 0.0;
@@ -374,6 +418,7 @@ __device__ __forceinline__ void chol_solve2(const Ctx2& c, double* x) {
     c.yt[i] = s0 + s1;
   }
   __syncthreads();
+#pragma unroll 1
   for (int j = threadIdx.x; j < n; j += QP_THREADS) {
     double s0 = 0.0, s1 = 0.0;
     int i = j;
@@ -384,15 +429,24 @@ __device__ __forceinline__ void chol_solve2(const Ctx2& c, double* x) {
   __syncthreads();
 }
 
-// Direction for (ru, rsig): du, dsig, dob (= Gb du).  K must hold the inverse factor for the current D.
-__device__ __forceinline__ void solve_direction2(const Ctx2& c, const double* ru, const double* rsig, bool sparse) {
-  slack_rhs_to_outputs2(c, rsig, c.wo);
+// Weights D -> Si/bh/Weff, K = H + A'DA, K <- inverse Cholesky factor.  One instantiation (not inlined).
+__device__ __noinline__ void factorise2() {
+  CTX2_LOCAL(c);
+  stage_weights2(c);
+  build_K2(c);
+  chol_inverse(c);
+}
+
+// Direction for (c.rhs, c.rsig): c.du, c.dsig, c.dob (= Gb du).  K must hold the inverse factor for the current D.
+__device__ __noinline__ void solve_direction2(int sparse) {
+  CTX2_LOCAL(c);
+  slack_rhs_to_outputs2(c, c.rsig, c.wo);
   __syncthreads();
-  apply_Gt2(c, c.wo, nullptr, 1.0, ru, 1.0, c.du, sparse);
+  apply_Gt2(c, c.wo, nullptr, 1.0, c.rhs, 1.0, c.du, sparse);
   __syncthreads();
   chol_solve2(c, c.du);
   stage_outputs2(c, c.du, c.dob, false);
   __syncthreads();
-  slack_backsolve2(c, rsig, c.dob, c.dsig);
+  slack_backsolve2(c, c.rsig, c.dob, c.dsig);
   __syncthreads();
 }

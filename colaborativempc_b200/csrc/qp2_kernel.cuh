@@ -15,6 +15,7 @@ __device__ __forceinline__ double pick9(const double* v, int idx) {  // v[idx] w
 // Prediction rows: x_t = cr_t + sum_j Gr_t[:, j] u_j for the kept state rows (one thread per input column,
 // plus one thread for the free response from x0).  Rows 0-3 (vx, e_y, x, y) go to the packed Gb, cost-only rows to Gx.
 __device__ __forceinline__ void setup_prediction2(const Ctx2& c, const DevParams& P, const double* x0) {
+#pragma unroll 1
   for (int j = threadIdx.x; j <= c.nu; j += QP_THREADS) {
     double v[9];
     if (j == c.nu) {
@@ -47,6 +48,7 @@ __device__ __forceinline__ double gr2(const Ctx2& c, int t, int r, int j) { retu
 // `ql` is an N x NR scratch (c.om .. c.dlam).  Ends with a barrier.
 __device__ __forceinline__ void setup_cost2(const Ctx2& c, const DevParams& P, const double* uold) {
   double* ql = c.om;
+#pragma unroll 1
   for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
     double* q = ql + t * c.NR;
     for (int r = 0; r < c.NR; ++r) q[r] = 0.0;
@@ -61,6 +63,7 @@ __device__ __forceinline__ void setup_cost2(const Ctx2& c, const DevParams& P, c
     q[3] += c.pxy[2 * t + 1];       // :422
   }
   __syncthreads();
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) {
     double s = 0.0;
     for (int t = j >> 1; t < c.N; ++t)
@@ -69,6 +72,7 @@ __device__ __forceinline__ void setup_cost2(const Ctx2& c, const DevParams& P, c
     if (j < 2) s -= 2.0 * (P.dR[j * 2 + 0] * uold[0] + P.dR[j * 2 + 1] * uold[1]);
     c.g[j] = s;
   }
+#pragma unroll 1
   for (int e = threadIdx.x; e < c.ntri; e += QP_THREADS) {
     const int ij = c.tri[e], i = ij >> 8, j = ij & 255;
     double s = 0.0;
@@ -116,14 +120,20 @@ __device__ __forceinline__ void rollout2(const Ctx2& c, const double* x0, double
 }
 
 __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid_constant__ DevParams P, const BatchPtrs io) {
-  extern __shared__ __align__(16) char smem_raw[];
   const int b = blockIdx.x;
   if (b >= io.B) return;
-  Ctx2 c;
-  carve_workspace2(c, smem_raw, P.N, P.nn, P.nrows);
   const int N = P.N, nn = P.nn;
-  int cnt = io.nbr_count ? io.nbr_count[b] : nn;
-  c.cnt = cnt < 0 ? 0 : (cnt > nn ? nn : cnt);
+  if (threadIdx.x == 0) {
+    Hdr2* hd = (Hdr2*)smem_fast;
+    int cnt = io.nbr_count ? io.nbr_count[b] : nn;
+    hd->N = N; hd->nn = nn; hd->NR = P.nrows; hd->cnt = cnt < 0 ? 0 : (cnt > nn ? nn : cnt);
+    hd->refine = P.refine; hd->pdas_first = P.pdas_first; hd->pdas_after = P.pdas_after; hd->ipm_max = P.ipm_max;
+    hd->n_rounds = 0; hd->n_ipm = 0;
+    hd->delta = P.delta; hd->cert_tol = P.cert_tol; hd->ipm_mu0 = P.ipm_mu0;
+    for (int i = 0; i < 9; ++i) hd->Qs[i] = P.Qs[i];
+  }
+  __syncthreads();
+  CTX2_LOCAL(c);
   const double* x0 = io.x0 + (size_t)b * NSTATE;
   const double* xprev = io.xprev + (size_t)b * io.xprev_rows * NSTATE;
   const double* uprev = io.uprev + (size_t)b * N * 2;
@@ -151,13 +161,14 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
     }
     return;
   }
+#pragma unroll 1
+  for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.bv[j] = row_valid2(c, j) ? row_h2_build(c, P, j) : 0.0;
   setup_prediction2(c, P, x0);
   __syncthreads();
   setup_cost2(c, P, uold);
 
   // ---------------- solve ----------------
-  int n_ipm = 0, n_rounds = 0;
-  const int status = solve_qp2(c, P, &n_ipm, &n_rounds);
+  const int status = solve_qp2(c);
 
   // ---------------- outputs (LPV_Planner.py:162-180 layout of res.x) ----------------
   setup_linearise(c, P, xprev, io.xprev_rows, uprev);  // A_k, B_k again: their block was reused by the solver
@@ -166,10 +177,12 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
   rollout2(c, x0, xs);
   if (io.z) {
     double* z = io.z + (size_t)b * n;
+#pragma unroll 1
     for (int w = threadIdx.x; w < 12 * (N + 1); w += QP_THREADS) {
       const int t = w / 12, r = w % 12;
       z[w] = r < 9 ? xs[9 * t + r] : (t == 0 ? 0.0 : c.sig[3 * (t - 1) + (r - 9)]);
     }
+#pragma unroll 1
     for (int j = threadIdx.x; j < 2 * N; j += QP_THREADS) {
       z[12 * (N + 1) + j] = c.u[j];
       z[12 * (N + 1) + 2 * N + j] = c.u[j] - (j < 2 ? uold[j] : c.u[j - 2]);
@@ -179,6 +192,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
   // objective 1/2 z'Pz + q'z (LPV_Planner.py:382-427)
   {
     double v = 0.0;
+#pragma unroll 1
     for (int t = threadIdx.x; t <= N; t += QP_THREADS) {
       const double* x = xs + 9 * t;
       double s = 0.0;
@@ -255,7 +269,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
   }
   if (threadIdx.x == 0) {
     if (io.status) io.status[b] = status;
-    if (io.iters) io.iters[b] = n_ipm;
-    if (io.pivots) io.pivots[b] = n_rounds;
+    if (io.iters) io.iters[b] = c.hd->n_ipm;
+    if (io.pivots) io.pivots[b] = c.hd->n_rounds;
   }
 }

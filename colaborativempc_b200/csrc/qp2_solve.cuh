@@ -7,32 +7,39 @@
 #include "qp2_engine.cuh"
 
 // res_j = (A v)_j - b_j for all rows, from inputs c.u and slacks c.sig.   Ends with a barrier.
-__device__ __forceinline__ void eval_residuals2(const Ctx2& c, const DevParams& P) {
+__device__ __noinline__ void eval_residuals2() {
+  CTX2_LOCAL(c);
   stage_outputs2(c, c.u, c.dob, true);
   __syncthreads();
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
-    c.res[j] = row_valid2(c, j) ? row_val2(c, j, c.dob, c.sig, c.u) - row_h2(c, P, j) : -1.0;
+    c.res[j] = row_valid2(c, j) ? row_val2(c, j, c.dob, c.sig, c.u) - c.bv[j] : -1.0;
   __syncthreads();
 }
 
 // One polish round on the active set c.act: equality-constrained QP solved by the proximal method of multipliers
 // with penalty 1/delta (OSQP's regularised KKT + iterative refinement, restated on the condensed system).
 // On exit: c.u, c.sig, c.lam (multipliers, zero on inactive rows), c.res.
-__device__ __forceinline__ void polish_round2(const Ctx2& c, const DevParams& P) {
-  const double Dv = 1.0 / P.delta;
+__device__ __forceinline__ void polish_round2(const Ctx2& c) {
+  const double Dv = 1.0 / c.hd->delta;
+  const double* Qs = c.hd->Qs;
+  const int refine = c.hd->refine;
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
     c.D[j] = (c.act[j] && row_valid2(c, j)) ? Dv : 0.0;
     c.lam[j] = 0.0;
   }
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) c.u[j] = 0.0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) c.sig[j] = 0.0;
   __syncthreads();
-  stage_weights2(c, P);
-  build_K2(c);
-  chol_inverse(c);
-  eval_residuals2(c, P);
-  for (int k = 0; k <= P.refine; ++k) {
+  factorise2();
+  eval_residuals2();
+#pragma unroll 1
+  for (int k = 0; k <= refine; ++k) {
     // gradient of the augmented Lagrangian: w = lam + D*res
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.om[j] = c.lam[j] + c.D[j] * c.res[j];
     __syncthreads();
     rows_to_stage2(c, c.om, c.wo, c.rsig);  // rsig <- A_s' w
@@ -40,37 +47,45 @@ __device__ __forceinline__ void polish_round2(const Ctx2& c, const DevParams& P)
     __syncthreads();
     // ru = -(H u + g + A_u' w)
     apply_Gt2(c, c.wo, c.om + c.Rs, -1.0, c.tv, -1.0, c.rhs, true);
+#pragma unroll 1
     for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
       const double s0 = c.sig[3 * t], s1 = c.sig[3 * t + 1], s2 = c.sig[3 * t + 2];
-      c.rsig[3 * t + 0] = -(2.0 * (P.Qs[0] * s0 + P.Qs[1] * s1 + P.Qs[2] * s2) + c.rsig[3 * t + 0]);
-      c.rsig[3 * t + 1] = -(2.0 * (P.Qs[3] * s0 + P.Qs[4] * s1 + P.Qs[5] * s2) + c.rsig[3 * t + 1]);
-      c.rsig[3 * t + 2] = -(2.0 * (P.Qs[6] * s0 + P.Qs[7] * s1 + P.Qs[8] * s2) + c.rsig[3 * t + 2]);
+      c.rsig[3 * t + 0] = -(2.0 * (Qs[0] * s0 + Qs[1] * s1 + Qs[2] * s2) + c.rsig[3 * t + 0]);
+      c.rsig[3 * t + 1] = -(2.0 * (Qs[3] * s0 + Qs[4] * s1 + Qs[5] * s2) + c.rsig[3 * t + 1]);
+      c.rsig[3 * t + 2] = -(2.0 * (Qs[6] * s0 + Qs[7] * s1 + Qs[8] * s2) + c.rsig[3 * t + 2]);
     }
     __syncthreads();
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) c.rhs[j] -= c.g[j];
     __syncthreads();
-    solve_direction2(c, c.rhs, c.rsig, true);
+    solve_direction2(1);
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) c.u[j] += c.du[j];
+#pragma unroll 1
     for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) c.sig[j] += c.dsig[j];
     __syncthreads();
-    eval_residuals2(c, P);
+    eval_residuals2();
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.lam[j] += c.D[j] * c.res[j];
     __syncthreads();
   }
 }
 
 // KKT certificate + primal-dual active-set update.  Returns 1 when (u, sig, lam) is optimal for the full QP.
-__device__ __forceinline__ int certify_update2(const Ctx2& c, const DevParams& P) {
+__device__ __forceinline__ int certify_update2(const Ctx2& c) {
+  const double cert_tol = c.hd->cert_tol;
   double lm = 0.0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) lm = fmax(lm, fabs(c.lam[j]));
   lm = 1.0 + block_max(lm, c.red);
   int changed = 0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
     if (!row_valid2(c, j)) continue;
-    const double h = row_h2(c, P, j);
+    const double h = c.bv[j];
     if (!c.act[j]) {
-      if (c.res[j] > P.cert_tol * (1.0 + fabs(h))) { c.act[j] = 1; changed = 1; }
-    } else if (c.lam[j] < -P.cert_tol * lm) {
+      if (c.res[j] > cert_tol * (1.0 + fabs(h))) { c.act[j] = 1; changed = 1; }
+    } else if (c.lam[j] < -cert_tol * lm) {
       c.act[j] = 0; changed = 1;
     }
   }
@@ -81,6 +96,7 @@ __device__ __forceinline__ int certify_update2(const Ctx2& c, const DevParams& P
 // order-independent 64-bit hash of the active set (sum of per-row mixes), all threads get the result
 __device__ __forceinline__ unsigned long long act_hash2(const Ctx2& c) {
   unsigned long long h = 0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
     if (c.act[j]) {
       unsigned long long x = (unsigned long long)(j + 1) * 0x9E3779B97F4A7C15ull;
@@ -100,12 +116,14 @@ __device__ __forceinline__ unsigned long long act_hash2(const Ctx2& c) {
 }
 
 // Up to `rounds` polish rounds; stops early on a certificate (returns 1) or when an active set repeats (0).
-__device__ __forceinline__ int pdas2(const Ctx2& c, const DevParams& P, int rounds, int* used) {
+__device__ __noinline__ int pdas2(int rounds) {
+  CTX2_LOCAL(c);
   int nh = 0;
+#pragma unroll 1
   for (int r = 0; r < rounds; ++r) {
-    polish_round2(c, P);
-    ++*used;
-    if (certify_update2(c, P)) return 1;
+    polish_round2(c);
+    if (threadIdx.x == 0) ++((Hdr2*)smem_fast)->n_rounds;
+    if (certify_update2(c)) return 1;
     const unsigned long long h = act_hash2(c);
     int cyc = 0;
     for (int i = 0; i < nh && i < 16; ++i) cyc |= (c.hist[i] == h);
@@ -120,13 +138,16 @@ __device__ __forceinline__ int pdas2(const Ctx2& c, const DevParams& P, int roun
 
 // dv for the current (D, rdu, rds) and complementarity right-hand side held in c.om (= rc/t - D*rp),
 // then A dv (c.dtt); caller finishes dt, dlam.
-__device__ __forceinline__ void ipm_direction2(const Ctx2& c, const DevParams& P) {
+__device__ __noinline__ void ipm_direction2() {
+  CTX2_LOCAL(c);
   rows_to_stage2(c, c.om, c.wo, c.rsig);
   __syncthreads();
   apply_Gt2(c, c.wo, c.om + c.Rs, 1.0, c.rdu, -1.0, c.rhs, false);  // -rdu + A_u' w
+#pragma unroll 1
   for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) c.rsig[j] -= c.rds[j];
   __syncthreads();
-  solve_direction2(c, c.rhs, c.rsig, false);
+  solve_direction2(0);
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
     c.dtt[j] = row_valid2(c, j) ? row_val2(c, j, c.dob, c.dsig, c.du) : 0.0;  // A dv
   __syncthreads();
@@ -134,6 +155,7 @@ __device__ __forceinline__ void ipm_direction2(const Ctx2& c, const DevParams& P
 
 __device__ __forceinline__ double step_to_boundary2(const Ctx2& c, const double* x, const double* dx) {
   double a = 1.0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
     if (row_valid2(c, j) && dx[j] < 0.0) a = fmin(a, -x[j] / dx[j]);
   return block_min(a, c.red);
@@ -141,35 +163,45 @@ __device__ __forceinline__ double step_to_boundary2(const Ctx2& c, const double*
 
 // Mehrotra predictor-corrector on the condensed QP down to complementarity mu_tol.
 // Returns 0 converged, 1 diverged (only a QP with infeasible hard rows does that), 2 iteration cap.
-__device__ __forceinline__ int ipm2(const Ctx2& c, const DevParams& P, double mu_tol, int* iters) {
+__device__ __noinline__ int ipm2(double mu_tol) {
+  CTX2_LOCAL(c);
+  const double* Qs = c.hd->Qs;
+  const int ipm_max = c.hd->ipm_max;
   const int m = c.N * (4 + c.cnt) + 4 * c.N;
   // ---- starting point: least squares with unit row weights, then shift into the cone
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.D[j] = row_valid2(c, j) ? 1.0 : 0.0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) c.u[j] = 0.0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) c.sig[j] = 0.0;
   __syncthreads();
-  stage_weights2(c, P);
-  build_K2(c);
-  chol_inverse(c);
-  eval_residuals2(c, P);
+  factorise2();
+  eval_residuals2();
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.om[j] = row_valid2(c, j) ? c.res[j] : 0.0;
   __syncthreads();
   rows_to_stage2(c, c.om, c.wo, c.rsig);
   __syncthreads();
   apply_Gt2(c, c.wo, c.om + c.Rs, -1.0, c.g, -1.0, c.rhs, false);
+#pragma unroll 1
   for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) c.rsig[j] = -c.rsig[j];
   __syncthreads();
-  solve_direction2(c, c.rhs, c.rsig, false);
+  solve_direction2(0);
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) c.u[j] = c.du[j];
+#pragma unroll 1
   for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) c.sig[j] = c.dsig[j];
   __syncthreads();
-  eval_residuals2(c, P);
+  eval_residuals2();
   {
     double mt = 1e300, ml = 1e300;
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
       if (row_valid2(c, j)) { mt = fmin(mt, -c.res[j]); ml = fmin(ml, c.res[j]); }
     mt = block_min(mt, c.red);
     ml = block_min(ml, c.red);
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
       if (!row_valid2(c, j)) { c.tt[j] = 1.0; c.lam[j] = 0.0; continue; }
       double t = -c.res[j], l = c.res[j];
@@ -180,48 +212,55 @@ __device__ __forceinline__ int ipm2(const Ctx2& c, const DevParams& P, double mu
     __syncthreads();
   }
   double v_g = 0.0;
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) v_g = fmax(v_g, fabs(c.g[j]));
   const double gmax = 1.0 + block_max(v_g, c.red);
-  for (int it = 0; it < P.ipm_max; ++it) {
+#pragma unroll 1
+  for (int it = 0; it < ipm_max; ++it) {
     // ---- residuals
-    eval_residuals2(c, P);
+    eval_residuals2();
     rows_to_stage2(c, c.lam, c.wo, c.rds);
     apply_H2(c, c.u, c.tv);
     __syncthreads();
     apply_Gt2(c, c.wo, c.lam + c.Rs, 1.0, c.tv, 1.0, c.rdu, false);
+#pragma unroll 1
     for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
       const double s0 = c.sig[3 * t], s1 = c.sig[3 * t + 1], s2 = c.sig[3 * t + 2];
-      c.rds[3 * t + 0] += 2.0 * (P.Qs[0] * s0 + P.Qs[1] * s1 + P.Qs[2] * s2);
-      c.rds[3 * t + 1] += 2.0 * (P.Qs[3] * s0 + P.Qs[4] * s1 + P.Qs[5] * s2);
-      c.rds[3 * t + 2] += 2.0 * (P.Qs[6] * s0 + P.Qs[7] * s1 + P.Qs[8] * s2);
+      c.rds[3 * t + 0] += 2.0 * (Qs[0] * s0 + Qs[1] * s1 + Qs[2] * s2);
+      c.rds[3 * t + 1] += 2.0 * (Qs[3] * s0 + Qs[4] * s1 + Qs[5] * s2);
+      c.rds[3 * t + 2] += 2.0 * (Qs[6] * s0 + Qs[7] * s1 + Qs[8] * s2);
     }
     __syncthreads();
     double v_mu = 0.0, v_rp = 0.0, v_rd = 0.0, v_obj = 0.0;
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
       if (row_valid2(c, j)) { v_mu = fma(c.lam[j], c.tt[j], v_mu); v_rp = fmax(v_rp, fabs(c.res[j] + c.tt[j])); }
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) {
       c.rdu[j] += c.g[j];
       v_rd = fmax(v_rd, fabs(c.rdu[j]));
       v_obj += c.u[j] * (0.5 * c.tv[j] + c.g[j]);
     }
+#pragma unroll 1
     for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) v_rd = fmax(v_rd, fabs(c.rds[j]));
     const double mu = block_sum(v_mu, c.red) / m;
     const double rp = block_max(v_rp, c.red), rd = block_max(v_rd, c.red);
     const double obj = fabs(block_sum(v_obj, c.red));
-    *iters = it;
+    if (threadIdx.x == 0) ++((Hdr2*)smem_fast)->n_ipm;
     if (!(mu == mu) || !(mu < 1e40) || !(rd < 1e40)) return 1;
     if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * gmax) return 0;
     // ---- factorise for D = lam / t
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.D[j] = row_valid2(c, j) ? c.lam[j] / c.tt[j] : 0.0;
     __syncthreads();
-    stage_weights2(c, P);
-    build_K2(c);
-    chol_inverse(c);
+    factorise2();
     // ---- predictor: rc = lam*t  ->  w = rc/t - D*rp = lam - D*(res + t)
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
       c.om[j] = row_valid2(c, j) ? c.lam[j] - c.D[j] * (c.res[j] + c.tt[j]) : 0.0;
     __syncthreads();
-    ipm_direction2(c, P);
+    ipm_direction2();
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
       if (!row_valid2(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
       const double dt = -(c.res[j] + c.tt[j]) - c.dtt[j];
@@ -231,11 +270,13 @@ __device__ __forceinline__ int ipm2(const Ctx2& c, const DevParams& P, double mu
     __syncthreads();
     double ap = step_to_boundary2(c, c.tt, c.dtt), ad = step_to_boundary2(c, c.lam, c.dlam);
     double v_aff = 0.0;
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
       if (row_valid2(c, j)) v_aff = fma(c.lam[j] + ad * c.dlam[j], c.tt[j] + ap * c.dtt[j], v_aff);
     const double mu_aff = block_sum(v_aff, c.red) / m;
     const double sr = mu_aff / mu, smu = sr * sr * sr * mu;
     // ---- corrector: rc = lam*t + dt_aff*dlam_aff - sigma*mu
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
       if (!row_valid2(c, j)) { c.om[j] = 0.0; continue; }
       const double rc = c.lam[j] * c.tt[j] + c.dtt[j] * c.dlam[j] - smu;
@@ -243,7 +284,8 @@ __device__ __forceinline__ int ipm2(const Ctx2& c, const DevParams& P, double mu
       c.om[j] = rc / c.tt[j] - c.D[j] * (c.res[j] + c.tt[j]);
     }
     __syncthreads();
-    ipm_direction2(c, P);
+    ipm_direction2();
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
       if (!row_valid2(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
       const double dt = -(c.res[j] + c.tt[j]) - c.dtt[j];
@@ -254,8 +296,11 @@ __device__ __forceinline__ int ipm2(const Ctx2& c, const DevParams& P, double mu
     __syncthreads();
     ap = fmin(1.0, 0.99 * step_to_boundary2(c, c.tt, c.dtt));
     ad = fmin(1.0, 0.99 * step_to_boundary2(c, c.lam, c.dlam));
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) c.u[j] = fma(ap, c.du[j], c.u[j]);
+#pragma unroll 1
     for (int j = threadIdx.x; j < 3 * c.N; j += QP_THREADS) c.sig[j] = fma(ap, c.dsig[j], c.sig[j]);
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
       c.tt[j] = fma(ap, c.dtt[j], c.tt[j]);
       c.lam[j] = fma(ad, c.dlam[j], c.lam[j]);
@@ -265,21 +310,21 @@ __device__ __forceinline__ int ipm2(const Ctx2& c, const DevParams& P, double mu
   return 2;
 }
 
-// Full solve.  Returns dmpc_status; *n_ipm / *n_rounds report the work done.
-__device__ __forceinline__ int solve_qp2(const Ctx2& c, const DevParams& P, int* n_ipm, int* n_rounds) {
+// Full solve.  Returns dmpc_status; the header counts the work done (n_rounds, n_ipm).
+__device__ __forceinline__ int solve_qp2(const Ctx2& c) {
+#pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = 0;
   __syncthreads();
-  *n_ipm = 0; *n_rounds = 0;
-  if (pdas2(c, P, P.pdas_first, n_rounds)) return DMPC_SOLVED;
-  double mu_tol = P.ipm_mu0;
+  if (pdas2(c.hd->pdas_first)) return DMPC_SOLVED;
+  double mu_tol = c.hd->ipm_mu0;
+#pragma unroll 1
   while (mu_tol > 1e-13) {
-    int its = 0;
-    const int rc = ipm2(c, P, mu_tol, &its);
-    *n_ipm += its;
+    const int rc = ipm2(mu_tol);
     if (rc == 1) return DMPC_PRIMAL_INFEASIBLE;
+#pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = row_valid2(c, j) && (c.lam[j] > c.tt[j]);
     __syncthreads();
-    if (pdas2(c, P, P.pdas_after, n_rounds)) return DMPC_SOLVED;
+    if (pdas2(c.hd->pdas_after)) return DMPC_SOLVED;
     mu_tol *= 1e-2;
   }
   return DMPC_MAX_ITER_REACHED;
