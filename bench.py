@@ -131,7 +131,7 @@ def run_reference(args):
     from colaborativempc_b200.track import TrackMap
     cfg, track = sc.shipped_config(), TrackMap("Highway")
     cores = len(os.sched_getaffinity(0))
-    sample = int(os.environ.get("DMPC_REF_SAMPLE", str(max(48, min(BATCH, 24 * cores)))))
+    sample = int(os.environ.get("DMPC_REF_SAMPLE", str(max(48, min(BATCH, 256 * cores)))))
     # same seeds as the GPU arm: the first `sample` QPs of its batch, warmed up by the oracle's certified solves
     ins = steady_state_inputs(oracle_solver(cfg, track, cores, exact=True), sample, cfg, track)
     solve = oracle_solver(cfg, track, cores, exact=False)
@@ -278,7 +278,7 @@ def run_gpu(args):
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "lpv_qp_solve_kernel", "kernel_ms": kern_ms,
+                "traffic": traffic, "kernel": "lpv_qp_fast_kernel" if eng.fast else "lpv_qp_solve_kernel", "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_qp": b_in + b_out,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback",
                 "note": "compulsory HBM traffic is 6.6 KB/QP; the kernel is bound by on-chip FP64 work (DESIGN.md), "

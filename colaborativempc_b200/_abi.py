@@ -103,7 +103,7 @@ def default_lib_path():
 
 EXPORTS = ["dmpc_default_options", "dmpc_version", "dmpc_create", "dmpc_destroy", "dmpc_last_error",
            "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
-           "dmpc_gather_neighbours", "dmpc_launch_count"]
+           "dmpc_gather_neighbours", "dmpc_launch_count", "dmpc_engine"]
 
 _lib = None
 
@@ -138,6 +138,8 @@ def load_library(path=None):
     lib.dmpc_shift_pack.restype = C.c_int
     lib.dmpc_gather_neighbours.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 5
     lib.dmpc_gather_neighbours.restype = C.c_int
+    lib.dmpc_engine.argtypes = [C.c_void_p]
+    lib.dmpc_engine.restype = C.c_int
     lib.dmpc_launch_count.argtypes = [C.c_void_p]
     lib.dmpc_launch_count.restype = C.c_int64
     if path == default_lib_path():

@@ -184,6 +184,8 @@ extern "C" int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt) {
   return DMPC_OK;
 }
 
+extern "C" int dmpc_engine(const dmpc_handle* h) { return h ? (h->fast ? DMPC_ENGINE_FAST : DMPC_ENGINE_GENERIC) : 0; }
+
 extern "C" int64_t dmpc_launch_count(const dmpc_handle* h) { return h ? h->launches : 0; }
 
 extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* stream) {

@@ -263,16 +263,28 @@ __device__ __forceinline__ int solve_qp(const Ctx& c, const DevParams& P, int* n
   __syncthreads();
   *n_ipm = 0; *n_rounds = 0;
   if (pdas(c, P, P.pdas_first, n_rounds)) return DMPC_SOLVED;
-  double mu_tol = P.ipm_mu0;
+  double mu_tol = P.ipm_mu0, mu_ok = 0.0;
   while (mu_tol > 1e-13) {
     int its = 0;
     const int rc = ipm(c, P, mu_tol, &its);
     *n_ipm += its;
-    if (rc == 1) return DMPC_PRIMAL_INFEASIBLE;
+    if (rc == 1) {  // divergence of the FIRST phase = infeasible hard rows; later (tighter) phases can only lose accuracy
+      if (mu_ok == 0.0) return DMPC_PRIMAL_INFEASIBLE;
+      break;
+    }
+    if (rc == 0) mu_ok = mu_tol;
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = row_valid(c, j) && (c.lam[j] > c.tt[j]);
     __syncthreads();
     if (pdas(c, P, P.pdas_after, n_rounds)) return DMPC_SOLVED;
     mu_tol *= 1e-2;
+  }
+  if (mu_ok > 0.0) {  // no active set certified (degenerate rows): hand back the tightest interior-point iterate
+    int its = 0;
+    ipm(c, P, mu_ok, &its);
+    *n_ipm += its;
+    for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) if (!row_valid(c, j)) c.lam[j] = 0.0;
+    __syncthreads();
+    return DMPC_SOLVED_INACCURATE;
   }
   return DMPC_MAX_ITER_REACHED;
 }

@@ -53,6 +53,7 @@ class BatchedPlannerLPV(object):
             self.lib.dmpc_destroy(self._h)
             self._h = None
             raise DmpcError("dmpc_create failed (%d): %s" % (rc, msg))
+        self.fast = self.lib.dmpc_engine(self._h) == 2  # packed shared-memory engine (qp2_*.cuh) vs generic
         self.n = 16 * self.N + 12
         self.m_in = (8 + self.nn) * self.N
         self.m_eq = 14 * self.N + 12

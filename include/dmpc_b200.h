@@ -147,6 +147,9 @@ int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A
                            const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
                            void* stream);
 
+/* Engine the handle runs on: DMPC_ENGINE_GENERIC or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
+int dmpc_engine(const dmpc_handle* h);
+
 /* Number of kernels the handle has launched so far (bench.py's gpu_launches claim). */
 int64_t dmpc_launch_count(const dmpc_handle* h);
 
