@@ -231,10 +231,10 @@ __device__ __noinline__ int ipm2(double mu_tol) {
       c.rds[3 * t + 2] += 2.0 * (Qs[6] * s0 + Qs[7] * s1 + Qs[8] * s2);
     }
     __syncthreads();
-    double v_mu = 0.0, v_rp = 0.0, v_rd = 0.0, v_obj = 0.0;
+    double v_mu = 0.0, v_rp = 0.0, v_rd = 0.0, v_obj = 0.0, v_lm = 0.0;
 #pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
-      if (row_valid2(c, j)) { v_mu = fma(c.lam[j], c.tt[j], v_mu); v_rp = fmax(v_rp, fabs(c.res[j] + c.tt[j])); }
+      if (row_valid2(c, j)) { v_mu = fma(c.lam[j], c.tt[j], v_mu); v_rp = fmax(v_rp, fabs(c.res[j] + c.tt[j])); v_lm = fmax(v_lm, c.lam[j]); }
 #pragma unroll 1
     for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) {
       c.rdu[j] += c.g[j];
@@ -246,9 +246,10 @@ __device__ __noinline__ int ipm2(double mu_tol) {
     const double mu = block_sum(v_mu, c.red) / m;
     const double rp = block_max(v_rp, c.red), rd = block_max(v_rd, c.red);
     const double obj = fabs(block_sum(v_obj, c.red));
+    const double lmax = block_max(v_lm, c.red);  // the dual residual carries the rounding of A' lam: scale with it
     if (threadIdx.x == 0) ++((Hdr2*)smem_fast)->n_ipm;
     if (!(mu == mu) || !(mu < 1e40) || !(rd < 1e40)) return 1;
-    if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * gmax) return 0;
+    if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * (gmax + lmax)) return 0;
     // ---- factorise for D = lam / t
 #pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.D[j] = row_valid2(c, j) ? c.lam[j] / c.tt[j] : 0.0;

@@ -187,9 +187,9 @@ __device__ __forceinline__ int ipm(const Ctx& c, const DevParams& P, double mu_t
       c.rds[3 * t + 2] += 2.0 * (P.Qs[6] * s0 + P.Qs[7] * s1 + P.Qs[8] * s2);
     }
     __syncthreads();
-    double v_mu = 0.0, v_rp = 0.0, v_rd = 0.0, v_obj = 0.0;
+    double v_mu = 0.0, v_rp = 0.0, v_rd = 0.0, v_obj = 0.0, v_lm = 0.0;
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS)
-      if (row_valid(c, j)) { v_mu = fma(c.lam[j], c.tt[j], v_mu); v_rp = fmax(v_rp, fabs(c.res[j] + c.tt[j])); }
+      if (row_valid(c, j)) { v_mu = fma(c.lam[j], c.tt[j], v_mu); v_rp = fmax(v_rp, fabs(c.res[j] + c.tt[j])); v_lm = fmax(v_lm, c.lam[j]); }
     for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) {
       c.rdu[j] += c.g[j];
       v_rd = fmax(v_rd, fabs(c.rdu[j]));
@@ -199,9 +199,10 @@ __device__ __forceinline__ int ipm(const Ctx& c, const DevParams& P, double mu_t
     const double mu = block_sum(v_mu, c.red) / m;
     const double rp = block_max(v_rp, c.red), rd = block_max(v_rd, c.red);
     const double obj = fabs(block_sum(v_obj, c.red));
+    const double lmax = block_max(v_lm, c.red);  // the dual residual carries the rounding of A' lam: scale with it
     *iters = it;
     if (!(mu == mu) || !(mu < 1e40) || !(rd < 1e40)) return 1;
-    if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * gmax) return 0;
+    if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * (gmax + lmax)) return 0;
     // ---- factorise for D = lam / t
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.D[j] = row_valid(c, j) ? c.lam[j] / c.tt[j] : 0.0;
     __syncthreads();

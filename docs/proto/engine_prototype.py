@@ -113,7 +113,7 @@ def ipm(qp, mu_tol=1e-7, maxit=40, verbose=False):
         mu=((ls*ts).sum()+(lb*tb).sum())/m
         obj=abs(0.5*u@qp.H@u+qp.g@u)
         if verbose: print(it,'rd %.2e rp %.2e mu %.2e'%(max(np.abs(rdu).max(),np.abs(rds).max()),max(np.abs(rps).max(),np.abs(rpb).max()),mu))
-        if mu<=mu_tol*(1+obj) and max(np.abs(rps).max(),np.abs(rpb).max())<=mu_tol*10 and max(np.abs(rdu).max(),np.abs(rds).max())<=mu_tol*(1+np.abs(qp.g).max())*10:
+        if mu<=mu_tol*(1+obj) and max(np.abs(rps).max(),np.abs(rpb).max())<=mu_tol*10 and max(np.abs(rdu).max(),np.abs(rds).max())<=mu_tol*(1+np.abs(qp.g).max()+max(ls.max(),lb.max()))*10:
             break
         Ds=ls/ts; Db=lb/tb
         def solve(rcs,rcb):

@@ -54,12 +54,13 @@ def _kkt_certificate(cfg, track, ins, out, b, N, nn):
     z = out["z"][b]
     y = np.concatenate([out["y_ineq"][b], out["y_eq"][b]])
     Az = A @ z
-    assert max((Az - u).max(), (l - Az).max()) < 1e-8
+    zsc = 1 + np.abs(z).max()  # the parity bar is 1e-6 RELATIVE: states reach |s| ~ 47 m, and a 50-step roll-out of the
+    assert max((Az - u).max(), (l - Az).max()) < TOL * zsc  # LPV dynamics amplifies rounding to ~1e-5 absolute
     m_in = out["y_ineq"].shape[1]
     ysc = 1 + np.abs(y).max()
     assert out["y_ineq"][b].min() >= -1e-9 * ysc
-    assert np.abs(Pm @ z + q + A.T @ y).max() < 1e-7 * (ysc + np.abs(q).max())
-    assert np.abs(y[:m_in] * (Az[:m_in] - u[:m_in])).max() < 1e-7 * ysc
+    assert np.abs(Pm @ z + q + A.T @ y).max() < TOL * (ysc + np.abs(q).max())
+    assert np.abs(y[:m_in] * (Az[:m_in] - u[:m_in])).max() < TOL * ysc * zsc
     assert abs(0.5 * z @ Pm @ z + q @ z - out["obj"][b]) < 1e-8 * (1 + abs(out["obj"][b]))
 
 
