@@ -27,13 +27,16 @@ struct Hdr2 {
   int n_rounds, n_ipm, pad0, pad1;
   double delta, cert_tol, ipm_mu0;
   double Qs[9];
+  double Qsi[9];  // (2 Qs)^-1, for the exact slack elimination of the Schur-complement rounds
 };
 
 extern __shared__ __align__(16) char smem_fast[];
 
 struct Ctx2 {
-  int N, nn, cnt, nu, NR, rst, Rs, RT, ntri;
+  int N, nn, cnt, nu, NR, rst, Rs, RT, ntri, WS, ldy;
   const Hdr2* hd;
+  double *Hi, *Y, *S, *lw, *rw;  // Schur rounds: L_H^-1 (packed), Y = L_H^-1 A_W' (nu x ldy), S (packed), lambda_W, rhs_W
+  int* wl;                       // rows of the working set
   double* bv;  // right-hand side b of every row (LPV_Planner.py:304-369)
   // problem data
   double *Gb, *Gx, *H, *K;
@@ -68,6 +71,13 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   c.K = take(kx > (size_t)c.ntri ? kx : (size_t)c.ntri);
   c.Gx = c.K;
   c.Acol = take(27 * N); c.Bcol = take(4 * N);
+  {  // Schur-round scratch aliases K + the linearisation block: largest working set (<= 32 rows) that fits
+    const size_t room = (size_t)((c.Acol + 31 * N) - c.K);
+    int ws = 32;
+    while (ws > 1 && (size_t)c.nu * (ws + 1) + (size_t)ws * (ws + 1) / 2 > room) --ws;
+    c.WS = ws; c.ldy = ws + 1;
+    c.Y = c.K; c.S = c.K + (size_t)c.nu * c.ldy;
+  }
   c.Z = c.Acol;
   c.eyb = take(N); c.pxy = take(2 * N);
   c.ax = take((size_t)N * nn); c.ay = take((size_t)N * nn); c.hh = take((size_t)N * nn);
@@ -80,6 +90,7 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   c.Weff = c.om;  // 10N <= 2 RT: only alive between stage_weights2 and build_K2, when om/dlam are dead
   c.Si = take(6 * N); c.bh = take(4 * N); c.wo = take(4 * N); c.dob = take(4 * N);
   c.rs = take(c.nu); c.lrow = take(2 * c.nu);
+  c.Hi = take(c.ntri); c.lw = take(32); c.rw = take(32); c.wl = (int*)take(16);
   c.red = take(8);
   c.hist = (unsigned long long*)take(16);
   c.redi = (int*)take(4);

@@ -3,7 +3,7 @@
 // (distributedPlanner/LPV_Planner.py:115-182) on chip.
 #pragma once
 #include "qp_setup.cuh"
-#include "qp2_solve.cuh"
+#include "qp2_schur.cuh"
 
 __device__ __forceinline__ double pick9(const double* v, int idx) {  // v[idx] without spilling v to local memory
   double r = v[0];
@@ -131,6 +131,15 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
     hd->n_rounds = 0; hd->n_ipm = 0;
     hd->delta = P.delta; hd->cert_tol = P.cert_tol; hd->ipm_mu0 = P.ipm_mu0;
     for (int i = 0; i < 9; ++i) hd->Qs[i] = P.Qs[i];
+    {  // (2 Qs)^-1 by cofactors (Qs symmetric positive definite, checked in dmpc_create)
+      const double a = 2 * P.Qs[0], b = 2 * P.Qs[1], cc = 2 * P.Qs[2], d = 2 * P.Qs[4], e = 2 * P.Qs[5], f = 2 * P.Qs[8];
+      const double c00 = d * f - e * e, c01 = cc * e - b * f, c02 = b * e - cc * d;
+      const double c11 = a * f - cc * cc, c12 = b * cc - a * e, c22 = a * d - b * b;
+      const double idet = 1.0 / (a * c00 + b * c01 + cc * c02);
+      hd->Qsi[0] = c00 * idet; hd->Qsi[1] = c01 * idet; hd->Qsi[2] = c02 * idet;
+      hd->Qsi[3] = c01 * idet; hd->Qsi[4] = c11 * idet; hd->Qsi[5] = c12 * idet;
+      hd->Qsi[6] = c02 * idet; hd->Qsi[7] = c12 * idet; hd->Qsi[8] = c22 * idet;
+    }
   }
   __syncthreads();
   CTX2_LOCAL(c);

@@ -311,33 +311,3 @@ __device__ __noinline__ int ipm2(double mu_tol) {
   return 2;
 }
 
-// Full solve.  Returns dmpc_status; the header counts the work done (n_rounds, n_ipm).
-__device__ __forceinline__ int solve_qp2(const Ctx2& c) {
-#pragma unroll 1
-  for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = 0;
-  __syncthreads();
-  if (pdas2(c.hd->pdas_first)) return DMPC_SOLVED;
-  double mu_tol = c.hd->ipm_mu0, mu_ok = 0.0;
-#pragma unroll 1
-  while (mu_tol > 1e-13) {
-    const int rc = ipm2(mu_tol);
-    if (rc == 1) {  // divergence of the FIRST phase = infeasible hard rows; later (tighter) phases can only lose accuracy
-      if (mu_ok == 0.0) return DMPC_PRIMAL_INFEASIBLE;
-      break;
-    }
-    if (rc == 0) mu_ok = mu_tol;
-#pragma unroll 1
-    for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = row_valid2(c, j) && (c.lam[j] > c.tt[j]);
-    __syncthreads();
-    if (pdas2(c.hd->pdas_after)) return DMPC_SOLVED;
-    mu_tol *= 1e-2;
-  }
-  if (mu_ok > 0.0) {  // no active set certified (degenerate rows): hand back the tightest interior-point iterate
-    ipm2(mu_ok);
-#pragma unroll 1
-    for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) if (!row_valid2(c, j)) c.lam[j] = 0.0;
-    __syncthreads();
-    return DMPC_SOLVED_INACCURATE;
-  }
-  return DMPC_MAX_ITER_REACHED;
-}
