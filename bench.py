@@ -247,6 +247,27 @@ def run_gpu(args):
     iters_mean = float(d_out["iters"].double().mean().item())
     rounds_mean = float(d_out["pivots"].double().mean().item())
 
+    # ---- the same steps with the cost-ordered launch off (blockIdx = QP index): what a cold, never-seen batch costs
+    unordered = None
+    if world == 1 and eng.fast:
+        eng.set_options(order_hint=0)
+        step()
+        torch.cuda.synchronize()
+        up = []
+        for _ in range(args.steps):
+            _flush_l2(torch, flush)
+            e0, e1 = ev(), ev()
+            e0.record()
+            step()
+            e1.record()
+            up.append((e0, e1))
+        torch.cuda.synchronize()
+        ums = float(np.mean([a.elapsed_time(b) for a, b in up]))
+        unordered = {"ms_per_step": ums, "value": BATCH / (ums * 1e-3), "unit": "QP/s"}
+        eng.set_options(order_hint=1)
+        step()
+        torch.cuda.synchronize()
+
     # ---- dominant kernel (lpv_qp_solve_kernel) timed alone on its launch stream, for the roofline object
     if world == 1:
         kern_ms = total_ms / args.steps
@@ -338,7 +359,11 @@ def run_gpu(args):
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload, "horizon": HORIZON, "nn": NN, "qp_per_step": qp_per_step,
                            "parallelism": par, "l2": "flushed between timed steps (256 MiB memset)",
-                           "outputs": "Solution z, planes, obj, status (duals off; parity tests run with duals on)"},
+                           "outputs": "Solution z, planes, obj, status (duals off; parity tests run with duals on)",
+                           "launch_order": "QPs start in decreasing order of the previous step's solve cost (dmpc_options."
+                                           "order_hint, scheduling only: every QP is solved from scratch every step); "
+                                           "`unordered` = same steps with the hint off"},
+                "unordered": unordered,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
                 "p50_step_ms": float(np.median(per_step)), "wall_ms_per_step": 1e3 * t_wall / args.steps,
                 "solved": n_ok, "qp_local": int(status.size), "ipm_iters_mean": iters_mean, "polish_rounds_mean": rounds_mean}

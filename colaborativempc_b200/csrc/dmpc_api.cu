@@ -18,6 +18,8 @@ struct dmpc_handle {
   size_t smem_bytes;
   long long gws_stride;
   double* d_gws;
+  int *d_cost, *d_order;  // fast engine: per-QP cost of the last call and the launch order derived from it
+  int order_B;            // batch size d_order is valid for (0: none yet)
   // staging for the host-buffer entry point
   char* d_stage;
   size_t stage_bytes;
@@ -41,7 +43,7 @@ extern "C" void dmpc_default_options(dmpc_options* o) {
   if (!o) return;
   o->polish_delta = 1e-9; o->cert_tol = 1e-9; o->ipm_mu0 = 1e-6;
   o->polish_refine = 4; o->pdas_first = 6; o->pdas_after = 4; o->ipm_max_iter = 60;
-  o->engine = DMPC_ENGINE_AUTO; o->reserved1 = 0;
+  o->engine = DMPC_ENGINE_AUTO; o->order_hint = 1;
 }
 
 static void apply_options(dmpc_handle* h) {
@@ -148,6 +150,8 @@ extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_
       return fail(h, DMPC_ERR_UNSUPPORTED, "horizon too long for the fast engine%s");
     if (fits && h->opt.engine != DMPC_ENGINE_GENERIC) {
       h->fast = 1; h->smem_bytes = sb2; h->gws_stride = 0;
+      CUDA_TRY(h, cudaMalloc(&h->d_cost, sizeof(int) * (size_t)max_batch));
+      CUDA_TRY(h, cudaMalloc(&h->d_order, sizeof(int) * (size_t)max_batch));
       CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb2));
       return DMPC_OK;
     }
@@ -169,6 +173,8 @@ extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_
 extern "C" void dmpc_destroy(dmpc_handle* h) {
   if (!h) return;
   if (h->d_gws) cudaFree(h->d_gws);
+  if (h->d_cost) cudaFree(h->d_cost);
+  if (h->d_order) cudaFree(h->d_order);
   if (h->d_stage) cudaFree(h->d_stage);
   delete h;
 }
@@ -202,8 +208,22 @@ extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* s
   bp.z = io->z; bp.planes = io->planes; bp.y_ineq = io->y_ineq; bp.y_eq = io->y_eq; bp.obj = io->obj;
   bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
   bp.gws = h->d_gws; bp.gws_stride = h->gws_stride;
-  if (h->fast) lpv_qp_fast_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
-  else lpv_qp_solve_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+  bp.order = nullptr; bp.cost = nullptr;
+  if (h->fast) {
+    // cost-ordered launch (dmpc_options.order_hint): this call starts its QPs in decreasing order of what the previous
+    // call of the same batch size spent on them - consecutive MPC steps of a scenario are alike, so the few
+    // interior-point QPs start first instead of becoming the tail of the grid.  Scheduling only; results do not change.
+    const bool hint = h->opt.order_hint != 0;
+    if (hint) { bp.cost = h->d_cost; if (h->order_B == io->B) bp.order = h->d_order; }
+    lpv_qp_fast_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+    if (hint) {
+      order_by_cost_kernel<<<1, ORDER_THREADS, 0, (cudaStream_t)stream>>>(h->d_cost, h->d_order, io->B);
+      h->order_B = io->B;
+      h->launches++;
+    }
+  } else {
+    lpv_qp_solve_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+  }
   h->launches++;
   CUDA_TRY(h, cudaGetLastError());
   return DMPC_OK;

@@ -46,6 +46,7 @@ struct Ctx2 {
   double *u, *rhs, *du, *tv, *rdu, *yt;
   double *lam, *tt, *D, *res, *om, *dlam, *dtt;
   double *sig, *dsig, *rsig, *rds;
+  double* sv;  // interior-point iterate kept between the phases of the mu ladder (nu + 3N + 2 RT)
   double *Weff, *Si, *bh, *wo, *dob;  // ro aliases wo, o aliases dob
   double *rs, *lrow;
   double* red;
@@ -90,7 +91,12 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   c.Weff = c.om;  // 10N <= 2 RT: only alive between stage_weights2 and build_K2, when om/dlam are dead
   c.Si = take(6 * N); c.bh = take(4 * N); c.wo = take(4 * N); c.dob = take(4 * N);
   c.rs = take(c.nu); c.lrow = take(2 * c.nu);
-  c.Hi = take(c.ntri); c.lw = take(32); c.rw = take(32); c.wl = (int*)take(16);
+  c.Hi = take(c.ntri);
+  {  // the Schur rounds are over (and L_H^-1 dead) once the interior-point phase starts
+    const size_t need = (size_t)c.nu + 3 * N + 2 * (size_t)c.RT;
+    c.sv = need <= (size_t)c.ntri ? c.Hi : take(need);
+  }
+  c.lw = take(32); c.rw = take(32); c.wl = (int*)take(16);
   c.red = take(8);
   c.hist = (unsigned long long*)take(16);
   c.redi = (int*)take(4);

@@ -120,8 +120,8 @@ __device__ __forceinline__ void rollout2(const Ctx2& c, const double* x0, double
 }
 
 __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid_constant__ DevParams P, const BatchPtrs io) {
-  const int b = blockIdx.x;
-  if (b >= io.B) return;
+  if (blockIdx.x >= io.B) return;
+  const int b = io.order ? io.order[blockIdx.x] : blockIdx.x;
   const int N = P.N, nn = P.nn;
   if (threadIdx.x == 0) {
     Hdr2* hd = (Hdr2*)smem_fast;
@@ -167,6 +167,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
       if (io.obj) io.obj[b] = qnan;
       if (io.iters) io.iters[b] = 0;
       if (io.pivots) io.pivots[b] = 0;
+      if (io.cost) io.cost[b] = 0;
     }
     return;
   }
@@ -280,5 +281,56 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
     if (io.status) io.status[b] = status;
     if (io.iters) io.iters[b] = c.hd->n_ipm;
     if (io.pivots) io.pivots[b] = c.hd->n_rounds;
+    if (io.cost) io.cost[b] = 24 * c.hd->n_ipm + c.hd->n_rounds;  // an interior-point iteration ~ 24 Schur rounds
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// order[] for the next call from this call's cost[]: a counting sort into 8 cost classes, most expensive class first,
+// QP index ascending inside a class (deterministic).  One CTA; each thread owns a contiguous chunk of the batch.
+// Only the launch order depends on it - every QP is solved from scratch on every call whatever the order.
+#define ORDER_THREADS 1024
+#define ORDER_CLASSES 8
+__device__ __forceinline__ int cost_class(int cst) {
+  return cst >= 24 * 16 ? 7 : cst >= 24 ? 6 : cst >= 12 ? 5 : cst >= 6 ? 4 : cst >= 4 ? 3 : cst >= 3 ? 2 : cst >= 2 ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(ORDER_THREADS, 1) order_by_cost_kernel(const int* __restrict__ cost, int* __restrict__ order, int B) {
+  __shared__ int wsum[ORDER_THREADS / 32];
+  __shared__ int base;
+  const int chunk = (B + ORDER_THREADS - 1) / ORDER_THREADS;
+  const int lo = min(B, (int)threadIdx.x * chunk), hi = min(B, lo + chunk);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+#pragma unroll 1
+  for (int cls = ORDER_CLASSES - 1; cls >= 0; --cls) {
+    int mine = 0;
+    for (int i = lo; i < hi; ++i) mine += (cost_class(cost[i]) == cls);
+    int incl = mine;  // inclusive scan over the block
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int v = wsum[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int w = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += w;
+      }
+      wsum[lane] = v;
+    }
+    __syncthreads();
+    int pos = base + incl - mine + (warp ? wsum[warp - 1] : 0);
+    for (int i = lo; i < hi; ++i)
+      if (cost_class(cost[i]) == cls) order[pos++] = i;
+    const int total = wsum[ORDER_THREADS / 32 - 1];
+    __syncthreads();
+    if (threadIdx.x == 0) base += total;
+    __syncthreads();
   }
 }

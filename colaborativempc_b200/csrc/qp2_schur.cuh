@@ -63,6 +63,98 @@ __device__ __forceinline__ double small_solve(const double* S, int w, double b) 
   return v;
 }
 
+// Block-wide arg-max of (v, idx) (ties -> smaller idx); all threads get the winner.  Scratch: c.red / c.asl.
+__device__ __forceinline__ int block_argmax(const Ctx2& c, double v, int idx, double* vmax) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double v2 = __shfl_xor_sync(0xffffffffu, v, o);
+    const int i2 = __shfl_xor_sync(0xffffffffu, idx, o);
+    if (v2 > v || (v2 == v && i2 < idx)) { v = v2; idx = i2; }
+  }
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) { c.red[threadIdx.x >> 5] = v; c.asl[threadIdx.x >> 5] = idx; }
+  __syncthreads();
+  double bv = c.red[0];
+  int bi = c.asl[0];
+#pragma unroll
+  for (int w = 1; w < QP_WARPS; ++w) {
+    const double v2 = c.red[w];
+    const int i2 = c.asl[w];
+    if (v2 > bv || (v2 == bv && i2 < bi)) { bv = v2; bi = i2; }
+  }
+  *vmax = bv;
+  return bi;
+}
+
+// Working-set update of the Schur rounds.  Returns 1 when (u, sig, lam) passes the KKT certificate, 2 when the set
+// cannot grow any further (overflow), 0 otherwise (c.act updated).
+//   normal mode: drop every row with a negative multiplier, add the violated rows - all of them if they fit in the WS
+//                slots, else the most violated ones;
+//   safe mode (after a repeated working set): one change per round - drop the most negative multiplier, else add the
+//                most violated row.
+__device__ __forceinline__ int schur_update(const Ctx2& c, int safe) {
+  const double cert_tol = c.hd->cert_tol;
+  double lm = 0.0;
+#pragma unroll 1
+  for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) lm = fmax(lm, fabs(c.lam[j]));
+  lm = 1.0 + block_max(lm, c.red);
+  double* score = c.om;  // > 0: violated inactive row (relative violation); < 0: active row with a negative multiplier
+  double cnt = 0.0;
+#pragma unroll 1
+  for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
+    double sc = 0.0;
+    if (row_valid2(c, j)) {
+      const double hs = 1.0 + fabs(c.bv[j]);
+      if (!c.act[j]) { if (c.res[j] > cert_tol * hs) { sc = c.res[j] / hs; cnt += 1.0; } }
+      else if (c.lam[j] < -cert_tol * lm) { sc = c.lam[j]; cnt += 4096.0; }
+      else cnt += 16777216.0;
+    }
+    score[j] = sc;
+  }
+  cnt = block_sum(cnt, c.red);
+  const long long total = (long long)cnt;  // three 12-bit counters in one exact FP64 sum (RT < 4096)
+  const int nviol = (int)(total & 4095), nneg = (int)((total >> 12) & 4095), nkeep = (int)(total >> 24);
+  if (nviol == 0 && nneg == 0) return 1;
+  if (!safe) {
+    const int room = c.WS - nkeep;
+    if (nviol <= room) {
+#pragma unroll 1
+      for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) { if (score[j] > 0.0) c.act[j] = 1; else if (score[j] < 0.0) c.act[j] = 0; }
+    } else {
+#pragma unroll 1
+      for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) if (score[j] < 0.0) c.act[j] = 0;
+      if (room <= 0 && nneg == 0) { __syncthreads(); return 2; }
+#pragma unroll 1
+      for (int k = 0; k < room; ++k) {
+        double v = 0.0, vm;
+        int bi = 0x7fffffff;
+#pragma unroll 1
+        for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) if (score[j] > v) { v = score[j]; bi = j; }
+        bi = block_argmax(c, v, bi, &vm);
+        if (threadIdx.x == 0) { c.act[bi] = 1; score[bi] = 0.0; }
+        __syncthreads();
+      }
+    }
+  } else {
+    double v = 0.0, vm;
+    int bi = 0x7fffffff;
+    if (nneg > 0) {
+#pragma unroll 1
+      for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) if (-score[j] > v) { v = -score[j]; bi = j; }
+      bi = block_argmax(c, v, bi, &vm);
+      if (threadIdx.x == 0) c.act[bi] = 0;
+    } else {
+      if (nkeep >= c.WS) return 2;
+#pragma unroll 1
+      for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) if (score[j] > v) { v = score[j]; bi = j; }
+      bi = block_argmax(c, v, bi, &vm);
+      if (threadIdx.x == 0) c.act[bi] = 1;
+    }
+  }
+  __syncthreads();
+  return 0;
+}
+
 // L_H^-1 -> c.Hi, unconstrained optimum u0 = -H^-1 g -> c.rdu.  Ends with a barrier.
 __device__ __noinline__ void schur_prepare2() {
   CTX2_LOCAL(c);
@@ -79,8 +171,8 @@ __device__ __noinline__ void schur_prepare2() {
 }
 
 // Up to `rounds` Schur-complement rounds from the working set c.act (all-zero at the first call).
-// Returns 1 certified (c.u, c.sig, c.lam, c.res final), 0 working set repeated / round cap, 2 working set too large or
-// S singular (c.act holds the current guess for the penalty rounds).
+// Returns 1 certified (c.u, c.sig, c.lam, c.res final), 0 round cap, 2 working set cannot grow within WS rows,
+// 3 S numerically singular (dependent hard rows; c.act holds the current guess for the penalty rounds).
 __device__ __noinline__ int schur_pdas2(int rounds) {
   CTX2_LOCAL(c);
   const double* Qsi = c.hd->Qsi;
@@ -101,18 +193,21 @@ __device__ __noinline__ int schur_pdas2(int rounds) {
 #pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) res0[j] = c.res[j];  // every row at (u0, sig = 0)
   __syncthreads();
-  int nh = 0;
+  int nh = 0, safe = 0;
 #pragma unroll 1
-  for (int r = 0; r < rounds; ++r) {
-    if (certify_update2(c)) return 1;
+  for (int r = 0; r < rounds + 40; ++r) {
     {
+      const int st = schur_update(c, safe);
+      if (st) return st;
+    }
+    if (!safe) {
       const unsigned long long h = act_hash2(c);
       int cyc = 0;
       for (int i = 0; i < nh && i < 16; ++i) cyc |= (c.hist[i] == h);
       __syncthreads();
-      if (threadIdx.x == 0 && nh < 16) c.hist[nh] = h;
+      if (threadIdx.x == 0) c.hist[nh & 15] = h;
       ++nh;
-      if (cyc) { __syncthreads(); return 0; }
+      if (cyc || r + 1 >= rounds) safe = 1;  // repeated working set (or too many rounds): one change per round from here
     }
     if (threadIdx.x == 0) {  // working-set list
       int w = 0;
@@ -123,7 +218,7 @@ __device__ __noinline__ int schur_pdas2(int rounds) {
     }
     __syncthreads();
     const int w = *nw;
-    if (w > c.WS) return 2;
+    if (w > c.WS) return 2;  // (cannot happen: schur_update keeps the set within WS)
     // ---- Y = L_H^-1 A_W'   (entry (rr, i) = row rr of L_H^-1 times row wl[i] of A)
 #pragma unroll 1
     for (int e = threadIdx.x; e < w * nu; e += QP_THREADS) {
@@ -189,7 +284,7 @@ __device__ __noinline__ int schur_pdas2(int rounds) {
       if (lane == 0) *sing = sg;
     }
     __syncthreads();
-    if (*sing) return 2;
+    if (*sing) return 3;
     // ---- back-substitute; up to two corrections of lam_W from the residual of the working-set rows
 #pragma unroll 1
     for (int pass = 0; pass < 3; ++pass) {
@@ -249,28 +344,31 @@ __device__ __forceinline__ int solve_qp2(const Ctx2& c) {
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = 0;
   __syncthreads();
   schur_prepare2();
-  {
-    const int rs = schur_pdas2(3 * c.hd->pdas_first);
-    if (rs == 1) return DMPC_SOLVED;
-    if (rs == 2 && pdas2(c.hd->pdas_first)) return DMPC_SOLVED;
-  }
+  const int rs = schur_pdas2(3 * c.hd->pdas_first);
+  if (rs == 1) return DMPC_SOLVED;
+  // singular S: the penalty rounds tolerate dependent rows.  Overflow / round cap: large or cycling working sets, for
+  // which the penalty rounds almost never certify either (measured) - straight to the interior-point phase.
+  if (rs == 3 && pdas2(c.hd->pdas_first)) return DMPC_SOLVED;
+  // Interior-point ladder: each phase CONTINUES from the iterate the previous one converged to (kept in c.sv: the
+  // active-set rounds in between overwrite u, sigma, lambda), so a tighter target costs a few iterations, not a restart.
   double mu_tol = c.hd->ipm_mu0, mu_ok = 0.0;
 #pragma unroll 1
   while (mu_tol > 1e-13) {
-    const int rc = ipm2(mu_tol);
+    const int rc = ipm2(mu_tol, mu_ok > 0.0);
     if (rc == 1) {  // divergence of the FIRST phase = infeasible hard rows; later (tighter) phases can only lose accuracy
       if (mu_ok == 0.0) return DMPC_PRIMAL_INFEASIBLE;
       break;
     }
-    if (rc == 0) mu_ok = mu_tol;
+    if (rc == 0) { mu_ok = mu_tol; ipm_keep2(c, 1); }
 #pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = row_valid2(c, j) && (c.lam[j] > c.tt[j]);
     __syncthreads();
     if (pdas2(c.hd->pdas_after)) return DMPC_SOLVED;
+    if (rc == 2) break;  // iteration cap: a tighter target from the same start would hit it again
     mu_tol *= 1e-2;
   }
   if (mu_ok > 0.0) {  // no active set certified (degenerate rows): hand back the tightest interior-point iterate
-    ipm2(mu_ok);
+    ipm_keep2(c, 0);
 #pragma unroll 1
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) if (!row_valid2(c, j)) c.lam[j] = 0.0;
     __syncthreads();

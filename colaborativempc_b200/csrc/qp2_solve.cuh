@@ -161,13 +161,33 @@ __device__ __forceinline__ double step_to_boundary2(const Ctx2& c, const double*
   return block_min(a, c.red);
 }
 
-// Mehrotra predictor-corrector on the condensed QP down to complementarity mu_tol.
+// Interior-point iterate (u, sigma, t, lambda) <-> c.sv.  Ends with a barrier.
+__device__ __forceinline__ void ipm_keep2(const Ctx2& c, int save) {
+  double* p = c.sv;
+  double* const v[4] = {c.u, c.sig, c.tt, c.lam};
+  const int len[4] = {c.nu, 3 * c.N, c.RT, c.RT};
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+#pragma unroll 1
+    for (int j = threadIdx.x; j < len[q]; j += QP_THREADS) {
+      if (save) p[j] = v[q][j];
+      else v[q][j] = p[j];
+    }
+    p += len[q];
+  }
+  __syncthreads();
+}
+
+// Mehrotra predictor-corrector on the condensed QP down to complementarity mu_tol.  warm: continue from the iterate
+// kept in c.sv (the previous, looser phase) instead of building a starting point.
 // Returns 0 converged, 1 diverged (only a QP with infeasible hard rows does that), 2 iteration cap.
-__device__ __noinline__ int ipm2(double mu_tol) {
+__device__ __noinline__ int ipm2(double mu_tol, int warm) {
   CTX2_LOCAL(c);
   const double* Qs = c.hd->Qs;
   const int ipm_max = c.hd->ipm_max;
   const int m = c.N * (4 + c.cnt) + 4 * c.N;
+  if (warm) ipm_keep2(c, 0);
+  else {
   // ---- starting point: least squares with unit row weights, then shift into the cone
 #pragma unroll 1
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.D[j] = row_valid2(c, j) ? 1.0 : 0.0;
@@ -210,6 +230,7 @@ __device__ __noinline__ int ipm2(double mu_tol) {
       c.tt[j] = fmax(t, 1e-8); c.lam[j] = fmax(l, 1e-8);
     }
     __syncthreads();
+  }
   }
   double v_g = 0.0;
 #pragma unroll 1

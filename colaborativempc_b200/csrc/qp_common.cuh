@@ -42,6 +42,11 @@ struct BatchPtrs {
   int *status, *iters, *pivots;
   double* gws;              // global workspace, gws_stride doubles per QP
   long long gws_stride;
+  // launch order of the fast engine: CTA i solves QP order[i] (nullptr = identity) and records what the solve cost in
+  // cost[]; order_by_cost_kernel turns that into the next call's order, most expensive first, so the few QPs that
+  // need the interior-point phase do not start at the end of the grid and become the tail of the launch
+  const int* order;
+  int* cost;
 };
 
 // ---------------------------------------------------------------------------------------------------
