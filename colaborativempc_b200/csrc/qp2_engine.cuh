@@ -315,110 +315,223 @@ __device__ __forceinline__ void slack_backsolve2(const Ctx2& c, const double* rs
 }
 
 // K = H + sum_{t active} Gb_t' Weff_t Gb_t + diag(box weights), packed lower.  Ends with a barrier.
+// Register-tiled, no staging buffer and no barrier inside: a thread owns 8 rows x 1 column of K (rows 8rb..8rb+7,
+// column j <= 8rb+7), walks the active stages that reach its rows (2(t+1) > 8rb), forms z = Weff_t Gb_t[:, j] (4 values)
+// and adds Gb_t[:, i]' z for its 8 rows.  Gb rows are read as double2 (all offsets are even).
 __device__ __forceinline__ void build_K2(const Ctx2& c) {
-  const int nas = *c.nas;
+  const int nas = *c.nas, nu = c.nu;
+  const int nrb = (nu + 7) >> 3;
+  int ntile = 0;
+  for (int rb = 0; rb < nrb; ++rb) ntile += min(nu, 8 * rb + 8);
 #pragma unroll 1
-  for (int e = threadIdx.x; e < c.ntri; e += QP_THREADS) {
-    const int ij = c.tri[e], i = ij >> 8, j = ij & 255;
-    double s = c.H[e];
-    if (i == j) {
-      const double* db = c.D + c.Rs + 4 * (i >> 1) + 2 * (i & 1);
-      s += db[0] + db[1];
+  for (int tile = threadIdx.x; tile < ntile; tile += QP_THREADS) {
+    int rb = 0, j = tile;
+    while (j >= min(nu, 8 * rb + 8)) { j -= min(nu, 8 * rb + 8); ++rb; }
+    const int i0 = 8 * rb;
+    double acc[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int i = i0 + r;
+      acc[r] = (i < nu && i >= j) ? c.H[TRI(i) + j] : 0.0;
+      if (i == j) {
+        const double* db = c.D + c.Rs + 4 * (i >> 1) + 2 * (i & 1);
+        acc[r] += db[0] + db[1];
+      }
     }
-    c.K[e] = s;
-  }
-  for (int c0 = 0; c0 < nas; c0 += ZCAP) {
-    const int nc = min(ZCAP, nas - c0);
-    __syncthreads();
-    // Z = Weff_t Gb_t for the stages of this chunk
-    for (int sc = 0; sc < nc; ++sc) {
-      const int t = c.asl[c0 + sc];
+#pragma unroll 1
+    for (int a = 0; a < nas; ++a) {
+      const int t = c.asl[a], len = 2 * (t + 1);
+      if (len <= i0 || len <= j) continue;
+      const double* gb = c.Gb + 4 * t * (t + 1);
       const double* we = c.Weff + 10 * t;
-      double* z = c.Z + (size_t)sc * 4 * c.nu;
-#pragma unroll 1
-      for (int j = threadIdx.x; j < 2 * (t + 1); j += QP_THREADS) {
-        const double g0 = GB(c, t, 0, j), g1 = GB(c, t, 1, j), g2 = GB(c, t, 2, j), g3 = GB(c, t, 3, j);
-        z[j] = we[0] * g0 + we[1] * g1 + we[2] * g2 + we[3] * g3;
-        z[c.nu + j] = we[1] * g0 + we[4] * g1 + we[5] * g2 + we[6] * g3;
-        z[2 * c.nu + j] = we[2] * g0 + we[5] * g1 + we[7] * g2 + we[8] * g3;
-        z[3 * c.nu + j] = we[3] * g0 + we[6] * g1 + we[8] * g2 + we[9] * g3;
+      const double g0 = gb[j], g1 = gb[len + j], g2 = gb[2 * len + j], g3 = gb[3 * len + j];
+      const double z0 = we[0] * g0 + we[1] * g1 + we[2] * g2 + we[3] * g3;
+      const double z1 = we[1] * g0 + we[4] * g1 + we[5] * g2 + we[6] * g3;
+      const double z2 = we[2] * g0 + we[5] * g1 + we[7] * g2 + we[8] * g3;
+      const double z3 = we[3] * g0 + we[6] * g1 + we[8] * g2 + we[9] * g3;
+      const double2* r0 = (const double2*)(gb + i0);
+      const double2* r1 = (const double2*)(gb + len + i0);
+      const double2* r2 = (const double2*)(gb + 2 * len + i0);
+      const double2* r3 = (const double2*)(gb + 3 * len + i0);
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        if (i0 + 2 * p < len) {
+          const double2 a0 = r0[p], a1 = r1[p], a2 = r2[p], a3 = r3[p];
+          acc[2 * p] = fma(a0.x, z0, fma(a1.x, z1, fma(a2.x, z2, fma(a3.x, z3, acc[2 * p]))));
+          acc[2 * p + 1] = fma(a0.y, z0, fma(a1.y, z1, fma(a2.y, z2, fma(a3.y, z3, acc[2 * p + 1]))));
+        }
       }
     }
-    __syncthreads();
-#pragma unroll 1
-    for (int e = threadIdx.x; e < c.ntri; e += QP_THREADS) {
-      const int ij = c.tri[e], i = ij >> 8, j = ij & 255;
-      double s = c.K[e];
-      for (int sc = 0; sc < nc; ++sc) {
-        const int t = c.asl[c0 + sc];
-        if (2 * (t + 1) <= i) continue;
-        const double* z = c.Z + (size_t)sc * 4 * c.nu + j;
-        s = fma(GB(c, t, 0, i), z[0], s);
-        s = fma(GB(c, t, 1, i), z[c.nu], s);
-        s = fma(GB(c, t, 2, i), z[2 * c.nu], s);
-        s = fma(GB(c, t, 3, i), z[3 * c.nu], s);
-      }
-      c.K[e] = s;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int i = i0 + r;
+      if (i < nu && i >= j) c.K[TRI(i) + j] = acc[r];
     }
   }
   __syncthreads();
 }
 
-// In place: K (SPD, packed lower) -> L^-1 (packed lower), K = L L'.  One barrier per pivot.  Non-positive pivots are
-// floored.  The trailing triangle of step k is walked through the tri[] table (item e' -> (i', j'), shifted by k+1),
-// so every lane of the updating warps has work; the remaining warps write row k of L^-1 over row k of K.
+// In place: K (SPD, packed lower) -> L^-1 (packed lower), K = L L'.  Blocked, 8 columns per step, three barriers per
+// step instead of one per pivot.  Step s (rows/columns b0 = 8s .. b0+bs-1):
+//   A  warp 0 factorises the bs x bs diagonal block in registers (one row per lane, shuffles) and inverts it (one column
+//      per lane); its inverse replaces the block.  Meanwhile the other warps form T = L[blk, <b0] * Linv[<b0, <b0] (rows
+//      of L^-1 above the block are final, the block's own row of L is final since the previous step's panel) in c.Z.
+//   B  panel: L[i, blk] = K[i, blk] * Lss^-T for the rows below; and row block of the inverse: Linv[blk, <b0] = -Lss^-1 T.
+//   C  trailing update K[i][j] -= L[i, blk] . L[j, blk] in 2x2 register tiles.
+// Non-positive pivots are floored.
 __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
   const int n = c.nu, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) {
-    double d = c.K[0];
-    if (!(d > 1e-300)) d = 1e-30;
-    c.rs[0] = rsqrt(d);
-  }
-  __syncthreads();
+  const unsigned full = 0xffffffffu;
+  double* T = c.Z;  // 8 x ldt
+  const int ldt = n;
 #pragma unroll 1
-  for (int k = 0; k < n; ++k) {
-    const double rsk = c.rs[k];
-    const int nl = k < 14 ? 1 : (k < 27 ? 2 : 3);  // warps on the L^-1 row; the others update the trailing block
-    if (warp < QP_WARPS - nl) {
-      const double invd = rsk * rsk;
-      const int m = n - 1 - k, items = (m * (m + 1)) >> 1, stride = 32 * (QP_WARPS - nl);
+  for (int b0 = 0; b0 < n; b0 += 8) {
+    const int bs = min(8, n - b0);
+    // ---------------- A
+    if (warp == 0) {
+      const bool own = lane < bs;
+      const double* row = c.K + TRI(b0 + (own ? lane : 0)) + b0;
+      double a[8], rsv[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) a[q] = (own && q <= lane) ? row[q] : (q == lane ? 1.0 : 0.0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        double d = __shfl_sync(full, a[k], k);
+        if (!(d > 1e-300)) d = 1e-30;
+        const double rk = rsqrt(d);
+        rsv[k] = rk;
+        const double lk = (lane == k) ? d * rk : a[k] * rk;
+#pragma unroll
+        for (int j = k + 1; j < 8; ++j) {
+          const double v = __shfl_sync(full, lk, j);
+          a[j] = fma(-lk, v, a[j]);
+        }
+        a[k] = lk;
+      }
+      // column `lane` of the inverse: x[i] = -(sum_{m<i} l_im x[m]) / l_ii, x[lane] = 1 / l_ll, zero above
+      double x[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int m = 0; m < i; ++m) {
+          const double v = __shfl_sync(full, a[m], i);
+          sacc = fma(v, x[m], sacc);
+        }
+        x[i] = (i == lane) ? rsv[i] : (i > lane ? -sacc * rsv[i] : 0.0);
+      }
+      if (own) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (i >= lane && i < bs) c.K[TRI(b0 + i) + b0 + lane] = x[i];
+      }
+    } else if (b0 > 0) {
+      // T[r][j] = sum_{k=j}^{b0-1} L[b0+r][k] Linv[k][j]; an item = (column j, half of the block's rows)
+#pragma unroll 1
+      for (int e = threadIdx.x - 32; e < 2 * b0; e += QP_THREADS - 32) {
+        const int j = e >> 1, rh = (e & 1) * 4;
+        if (rh >= bs) continue;
+        const double* l0 = c.K + TRI(b0 + rh);  // rows past the block (bs < 8) repeat its last row; never stored
+        const double* l1 = c.K + TRI(b0 + min(rh + 1, bs - 1));
+        const double* l2 = c.K + TRI(b0 + min(rh + 2, bs - 1));
+        const double* l3 = c.K + TRI(b0 + min(rh + 3, bs - 1));
+        double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+        int tk = TRI(j) + j;
 #pragma unroll 2
-      for (int e = threadIdx.x; e < items; e += stride) {
-        const int ij = c.tri[e], i = k + 1 + (ij >> 8), j = k + 1 + (ij & 255);
-        const int ti = TRI(i);
-        const double v = fma(-c.K[ti + k] * invd, c.K[TRI(j) + k], c.K[ti + j]);
-        c.K[ti + j] = v;
-        if (e == 0) {  // (i, j) = (k+1, k+1): next pivot
-          double d = v;
-          if (!(d > 1e-300)) d = 1e-30;
-          c.rs[k + 1] = rsqrt(d);
+        for (int k = j; k < b0; ++k) {
+          const double v = c.K[tk];
+          tk += k + 1;
+          t0 = fma(l0[k], v, t0);
+          t1 = fma(l1[k], v, t1);
+          t2 = fma(l2[k], v, t2);
+          t3 = fma(l3[k], v, t3);
         }
-      }
-    } else {
-      const int lw = warp - (QP_WARPS - nl);  // 0 .. nl-1
-      // stage row k+1 of L (scaled) for the next step; all of its entries are final already
-      if (lw == 0 && k + 1 < n) {
-        double* ln = c.lrow + ((k + 1) & 1) * n;
-        const double* row = c.K + TRI(k + 1);
-        for (int j = lane; j <= k; j += 32) ln[j] = row[j] * c.rs[j];
-      }
-      // row k of L^-1:  Linv[k][t] = -(sum_{j=t}^{k-1} L[k][j] Linv[j][t]) / L[k][k]
-      const double* lk = c.lrow + (k & 1) * n;
-      for (int t = lane + 32 * lw; t <= k; t += 32 * nl) {
-        double s0 = 0.0, s1 = 0.0;
-        int j = t, tj = TRI(t) + t;
-#pragma unroll 1
-        for (; j + 1 < k; j += 2) {
-          s0 = fma(lk[j], c.K[tj], s0);
-          tj += j + 1;
-          s1 = fma(lk[j + 1], c.K[tj], s1);
-          tj += j + 2;
-        }
-        if (j < k) s0 = fma(lk[j], c.K[tj], s0);
-        c.K[TRI(k) + t] = (t == k) ? rsk : -(s0 + s1) * rsk;
+        if (rh < bs) T[(rh + 0) * ldt + j] = t0;
+        if (rh + 1 < bs) T[(rh + 1) * ldt + j] = t1;
+        if (rh + 2 < bs) T[(rh + 2) * ldt + j] = t2;
+        if (rh + 3 < bs) T[(rh + 3) * ldt + j] = t3;
       }
     }
     __syncthreads();
+    // ---------------- B
+    {
+      const int mrows = n - b0 - bs;
+      const int npan = 4 * mrows;  // (row, column pair); the four threads of a row sit in one warp
+      const int nit = (npan + b0 + QP_THREADS - 1) / QP_THREADS;
+#pragma unroll 1
+      for (int it = 0; it < nit; ++it) {
+        const int e = threadIdx.x + it * QP_THREADS;
+        const bool pan = e < npan;
+        const int i = b0 + bs + (e >> 2), cp = (e & 3) * 2;
+        double* kr = c.K + TRI(pan ? i : 0) + b0;
+        double kv[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) kv[q] = (pan && q < bs && q <= cp + 1) ? kr[q] : 0.0;
+        __syncwarp();  // in place: every thread of the row has read before any of them writes
+        if (pan) {
+          // L[i][b0+cc] = sum_{m<=cc} K[i][b0+m] Li[cc][m]
+          if (cp < bs) {
+            const double* li0 = c.K + TRI(b0 + cp) + b0;
+            double o0 = 0.0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) if (q <= cp) o0 = fma(kv[q], li0[q], o0);
+            kr[cp] = o0;
+          }
+          if (cp + 1 < bs) {
+            const double* li1 = c.K + TRI(b0 + cp + 1) + b0;
+            double o1 = 0.0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) if (q <= cp + 1) o1 = fma(kv[q], li1[q], o1);
+            kr[cp + 1] = o1;
+          }
+        } else if (e < npan + b0) {
+          const int j = e - npan;  // column of the inverse's row block
+          double tv[8];
+#pragma unroll
+          for (int r = 0; r < 8; ++r) tv[r] = r < bs ? T[r * ldt + j] : 0.0;
+#pragma unroll
+          for (int r = 0; r < 8; ++r) {
+            if (r < bs) {
+              const double* li = c.K + TRI(b0 + r) + b0;
+              double o = 0.0;
+#pragma unroll
+              for (int q = 0; q < 8; ++q) if (q <= r) o = fma(li[q], tv[q], o);
+              c.K[TRI(b0 + r) + j] = -o;
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---------------- C
+    const int m2 = (n - b0 - bs) >> 1;  // trailing rows / 2 (n and b0 + bs are even)
+    if (m2 > 0) {
+      const int base = b0 + bs, ntl = (m2 * (m2 + 1)) >> 1;
+#pragma unroll 1
+      for (int e = threadIdx.x; e < ntl; e += QP_THREADS) {
+        const int ij = c.tri[e], i = base + 2 * (ij >> 8), j = base + 2 * (ij & 255);
+        const double* li0 = c.K + TRI(i) + b0;
+        const double* li1 = li0 + i + 1;
+        const double* lj0 = c.K + TRI(j) + b0;
+        const double* lj1 = lj0 + j + 1;
+        double s00 = 0.0, s01 = 0.0, s10 = 0.0, s11 = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < bs) {
+            const double a0 = li0[q], a1 = li1[q], b0v = lj0[q], b1v = lj1[q];
+            s00 = fma(a0, b0v, s00); s01 = fma(a0, b1v, s01);
+            s10 = fma(a1, b0v, s10); s11 = fma(a1, b1v, s11);
+          }
+        }
+        double* k0 = c.K + TRI(i) + j;
+        double* k1 = k0 + i + 1;
+        k0[0] -= s00;
+        if (i != j) k0[1] -= s01;
+        k1[0] -= s10;
+        k1[1] -= s11;
+      }
+      __syncthreads();
+    }
   }
 }
 
