@@ -75,7 +75,8 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   {  // Schur-round scratch aliases K + the linearisation block: largest working set (<= 32 rows) that fits
     const size_t room = (size_t)((c.Acol + 31 * N) - c.K);
     int ws = 32;
-    while (ws > 1 && (size_t)c.nu * (ws + 1) + (size_t)ws * (ws + 1) / 2 > room) --ws;
+    while (ws > 1 && ((size_t)c.nu * (ws + 1) + (size_t)ws * (ws + 1) / 2 > room || 8 * ws > 2 * c.RT)) --ws;  // 8 x ws
+    // scratch of the S factorisation lives in dlam/dtt
     c.WS = ws; c.ldy = ws + 1;
     c.Y = c.K; c.S = c.K + (size_t)c.nu * c.ldy;
   }
@@ -378,11 +379,13 @@ __device__ __forceinline__ void build_K2(const Ctx2& c) {
 //      of L^-1 above the block are final, the block's own row of L is final since the previous step's panel) in c.Z.
 //   B  panel: L[i, blk] = K[i, blk] * Lss^-T for the rows below; and row block of the inverse: Linv[blk, <b0] = -Lss^-1 T.
 //   C  trailing update K[i][j] -= L[i, blk] . L[j, blk] in 2x2 register tiles.
-// Non-positive pivots are floored.
-__device__ __forceinline__ void chol_inverse(const Ctx2& c) {
-  const int n = c.nu, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+// Non-positive pivots are floored.  With d0 (the diagonal before the factorisation) a pivot below 1e-11 of its original
+// diagonal entry sets *sing (numerically dependent rows); the factorisation still runs to the end.
+// A: packed lower n x n (any n >= 1), T: 8 x n scratch, tri: the (i << 8 | j) table of packed-lower indices.
+__device__ __forceinline__ void chol_inverse_blk(double* A, const int n, double* T, const unsigned short* tri,
+                                                 const double* d0, int* sing) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned full = 0xffffffffu;
-  double* T = c.Z;  // 8 x ldt
   const int ldt = n;
 #pragma unroll 1
   for (int b0 = 0; b0 < n; b0 += 8) {
@@ -390,13 +393,14 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
     // ---------------- A
     if (warp == 0) {
       const bool own = lane < bs;
-      const double* row = c.K + TRI(b0 + (own ? lane : 0)) + b0;
+      const double* row = A + TRI(b0 + (own ? lane : 0)) + b0;
       double a[8], rsv[8];
 #pragma unroll
       for (int q = 0; q < 8; ++q) a[q] = (own && q <= lane) ? row[q] : (q == lane ? 1.0 : 0.0);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         double d = __shfl_sync(full, a[k], k);
+        if (d0 && k < bs && lane == 0 && !(d > 1e-11 * d0[b0 + k])) *sing = 1;
         if (!(d > 1e-300)) d = 1e-30;
         const double rk = rsqrt(d);
         rsv[k] = rk;
@@ -423,7 +427,7 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
       if (own) {
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          if (i >= lane && i < bs) c.K[TRI(b0 + i) + b0 + lane] = x[i];
+          if (i >= lane && i < bs) A[TRI(b0 + i) + b0 + lane] = x[i];
       }
     } else if (b0 > 0) {
       // T[r][j] = sum_{k=j}^{b0-1} L[b0+r][k] Linv[k][j]; an item = (column j, half of the block's rows)
@@ -431,15 +435,15 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
       for (int e = threadIdx.x - 32; e < 2 * b0; e += QP_THREADS - 32) {
         const int j = e >> 1, rh = (e & 1) * 4;
         if (rh >= bs) continue;
-        const double* l0 = c.K + TRI(b0 + rh);  // rows past the block (bs < 8) repeat its last row; never stored
-        const double* l1 = c.K + TRI(b0 + min(rh + 1, bs - 1));
-        const double* l2 = c.K + TRI(b0 + min(rh + 2, bs - 1));
-        const double* l3 = c.K + TRI(b0 + min(rh + 3, bs - 1));
+        const double* l0 = A + TRI(b0 + rh);  // rows past the block (bs < 8) repeat its last row; never stored
+        const double* l1 = A + TRI(b0 + min(rh + 1, bs - 1));
+        const double* l2 = A + TRI(b0 + min(rh + 2, bs - 1));
+        const double* l3 = A + TRI(b0 + min(rh + 3, bs - 1));
         double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
         int tk = TRI(j) + j;
 #pragma unroll 2
         for (int k = j; k < b0; ++k) {
-          const double v = c.K[tk];
+          const double v = A[tk];
           tk += k + 1;
           t0 = fma(l0[k], v, t0);
           t1 = fma(l1[k], v, t1);
@@ -463,7 +467,7 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
         const int e = threadIdx.x + it * QP_THREADS;
         const bool pan = e < npan;
         const int i = b0 + bs + (e >> 2), cp = (e & 3) * 2;
-        double* kr = c.K + TRI(pan ? i : 0) + b0;
+        double* kr = A + TRI(pan ? i : 0) + b0;
         double kv[8];
 #pragma unroll
         for (int q = 0; q < 8; ++q) kv[q] = (pan && q < bs && q <= cp + 1) ? kr[q] : 0.0;
@@ -471,14 +475,14 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
         if (pan) {
           // L[i][b0+cc] = sum_{m<=cc} K[i][b0+m] Li[cc][m]
           if (cp < bs) {
-            const double* li0 = c.K + TRI(b0 + cp) + b0;
+            const double* li0 = A + TRI(b0 + cp) + b0;
             double o0 = 0.0;
 #pragma unroll
             for (int q = 0; q < 8; ++q) if (q <= cp) o0 = fma(kv[q], li0[q], o0);
             kr[cp] = o0;
           }
           if (cp + 1 < bs) {
-            const double* li1 = c.K + TRI(b0 + cp + 1) + b0;
+            const double* li1 = A + TRI(b0 + cp + 1) + b0;
             double o1 = 0.0;
 #pragma unroll
             for (int q = 0; q < 8; ++q) if (q <= cp + 1) o1 = fma(kv[q], li1[q], o1);
@@ -492,11 +496,11 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
 #pragma unroll
           for (int r = 0; r < 8; ++r) {
             if (r < bs) {
-              const double* li = c.K + TRI(b0 + r) + b0;
+              const double* li = A + TRI(b0 + r) + b0;
               double o = 0.0;
 #pragma unroll
               for (int q = 0; q < 8; ++q) if (q <= r) o = fma(li[q], tv[q], o);
-              c.K[TRI(b0 + r) + j] = -o;
+              A[TRI(b0 + r) + j] = -o;
             }
           }
         }
@@ -504,16 +508,17 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
     }
     __syncthreads();
     // ---------------- C
-    const int m2 = (n - b0 - bs) >> 1;  // trailing rows / 2 (n and b0 + bs are even)
+    const int m2 = (n - b0 - bs + 1) >> 1;  // 2 x 2 tiles of the trailing block (the last one is 1 row short for odd sizes)
     if (m2 > 0) {
       const int base = b0 + bs, ntl = (m2 * (m2 + 1)) >> 1;
 #pragma unroll 1
       for (int e = threadIdx.x; e < ntl; e += QP_THREADS) {
-        const int ij = c.tri[e], i = base + 2 * (ij >> 8), j = base + 2 * (ij & 255);
-        const double* li0 = c.K + TRI(i) + b0;
-        const double* li1 = li0 + i + 1;
-        const double* lj0 = c.K + TRI(j) + b0;
-        const double* lj1 = lj0 + j + 1;
+        const int ij = tri[e], i = base + 2 * (ij >> 8), j = base + 2 * (ij & 255);
+        const bool i1 = i + 1 < n;
+        const double* li0 = A + TRI(i) + b0;
+        const double* li1 = i1 ? li0 + i + 1 : li0;
+        const double* lj0 = A + TRI(j) + b0;
+        const double* lj1 = (j + 1 < n) ? lj0 + j + 1 : lj0;
         double s00 = 0.0, s01 = 0.0, s10 = 0.0, s11 = 0.0;
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
@@ -523,16 +528,30 @@ __device__ __forceinline__ void chol_inverse(const Ctx2& c) {
             s10 = fma(a1, b0v, s10); s11 = fma(a1, b1v, s11);
           }
         }
-        double* k0 = c.K + TRI(i) + j;
-        double* k1 = k0 + i + 1;
+        double* k0 = A + TRI(i) + j;
         k0[0] -= s00;
         if (i != j) k0[1] -= s01;
-        k1[0] -= s10;
-        k1[1] -= s11;
+        if (i1) {
+          double* k1 = k0 + i + 1;
+          k1[0] -= s10;
+          k1[1] -= s11;
+        }
       }
       __syncthreads();
     }
   }
+}
+
+// The one instantiation of the blocked factorisation (its unrolled register blocks are ~50 KB of code): operands are
+// passed as offsets (in doubles) into the workspace so that every access stays a shared-memory access.
+// d0_off < 0: no dependence test; else *(c.redi + 3) is set when a pivot collapses.
+__device__ __noinline__ void chol_inverse_sh(int a_off, int n, int t_off, int d0_off) {
+  CTX2_LOCAL(c);
+  double* base = c.Gb;  // first array of the workspace
+  chol_inverse_blk(base + a_off, n, base + t_off, c.tri, d0_off >= 0 ? base + d0_off : nullptr, c.redi + 3);
+}
+__device__ __forceinline__ void chol_inverse(const Ctx2& c) {
+  chol_inverse_sh((int)(c.K - c.Gb), c.nu, (int)(c.Z - c.Gb), -1);
 }
 
 // x <- K^-1 x with K^-1 = Linv' Linv (Linv packed lower in c.K).  Ends with a barrier.

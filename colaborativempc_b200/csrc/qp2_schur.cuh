@@ -63,6 +63,26 @@ __device__ __forceinline__ double small_solve(const double* S, int w, double b) 
   return v;
 }
 
+// x = S^-1 b from the inverse factor left in S by chol_inverse_blk (S^-1 = Linv' Linv); warp 0, lane i passes b_i
+// and receives x_i (w <= 32).
+__device__ __forceinline__ double inv_solve(const double* S, int w, double b) {
+  const int lane = threadIdx.x & 31;
+  const double* row = S + TRI(lane < w ? lane : 0);
+  double y = 0.0;
+#pragma unroll 1
+  for (int j = 0; j < w; ++j) {
+    const double bj = __shfl_sync(0xffffffffu, b, j);
+    if (j <= lane && lane < w) y = fma(row[j], bj, y);
+  }
+  double x = 0.0;
+#pragma unroll 1
+  for (int i = 0; i < w; ++i) {
+    const double yi = __shfl_sync(0xffffffffu, y, i);
+    if (i >= lane && lane < w) x = fma(S[TRI(i) + lane], yi, x);
+  }
+  return x;
+}
+
 // Block-wide arg-max of (v, idx) (ties -> smaller idx); all threads get the winner.  Scratch: c.red / c.asl.
 __device__ __forceinline__ int block_argmax(const Ctx2& c, double v, int idx, double* vmax) {
 #pragma unroll
@@ -105,15 +125,17 @@ __device__ __forceinline__ int schur_update(const Ctx2& c, int safe) {
     double sc = 0.0;
     if (row_valid2(c, j)) {
       const double hs = 1.0 + fabs(c.bv[j]);
-      if (!c.act[j]) { if (c.res[j] > cert_tol * hs) { sc = c.res[j] / hs; cnt += 1.0; } }
+      if (!(fabs(c.res[j]) < 1e300) || !(fabs(c.lam[j]) < 1e300)) cnt += 68719476736.0;  // NaN / inf never certifies
+      else if (!c.act[j]) { if (c.res[j] > cert_tol * hs) { sc = c.res[j] / hs; cnt += 1.0; } }
       else if (c.lam[j] < -cert_tol * lm) { sc = c.lam[j]; cnt += 4096.0; }
       else cnt += 16777216.0;
     }
     score[j] = sc;
   }
   cnt = block_sum(cnt, c.red);
-  const long long total = (long long)cnt;  // three 12-bit counters in one exact FP64 sum (RT < 4096)
-  const int nviol = (int)(total & 4095), nneg = (int)((total >> 12) & 4095), nkeep = (int)(total >> 24);
+  const long long total = (long long)cnt;  // four 12-bit counters in one exact FP64 sum (RT < 4096)
+  const int nviol = (int)(total & 4095), nneg = (int)((total >> 12) & 4095), nkeep = (int)((total >> 24) & 4095);
+  if ((total >> 36) != 0) return 2;  // non-finite iterate: leave the rounds
   if (nviol == 0 && nneg == 0) return 1;
   if (!safe) {
     const int room = c.WS - nkeep;
@@ -173,7 +195,7 @@ __device__ __noinline__ void schur_prepare2() {
 // Up to `rounds` Schur-complement rounds from the working set c.act (all-zero at the first call).
 // Returns 1 certified (c.u, c.sig, c.lam, c.res final), 0 round cap, 2 working set cannot grow within WS rows,
 // 3 S numerically singular (dependent hard rows; c.act holds the current guess for the penalty rounds).
-__device__ __noinline__ int schur_pdas2(int rounds) {
+__device__ __noinline__ int schur_pdas2(int rounds, int safe_rounds) {
   CTX2_LOCAL(c);
   const double* Qsi = c.hd->Qsi;
   const double cert_tol = c.hd->cert_tol;
@@ -195,7 +217,7 @@ __device__ __noinline__ int schur_pdas2(int rounds) {
   __syncthreads();
   int nh = 0, safe = 0;
 #pragma unroll 1
-  for (int r = 0; r < rounds + 40; ++r) {
+  for (int r = 0; r < rounds + safe_rounds; ++r) {
     {
       const int st = schur_update(c, safe);
       if (st) return st;
@@ -209,12 +231,19 @@ __device__ __noinline__ int schur_pdas2(int rounds) {
       ++nh;
       if (cyc || r + 1 >= rounds) safe = 1;  // repeated working set (or too many rounds): one change per round from here
     }
-    if (threadIdx.x == 0) {  // working-set list
+    if (warp == 0) {  // working-set list, rows ascending (ballot compaction)
       int w = 0;
-      for (int j = 0; j < c.RT; ++j)
-        if (c.act[j]) { if (w < c.WS) c.wl[w] = j; ++w; }
-      *nw = w;
-      ++((Hdr2*)smem_fast)->n_rounds;
+#pragma unroll 1
+      for (int j0 = 0; j0 < c.RT; j0 += 32) {
+        const int j = j0 + lane;
+        const unsigned m = __ballot_sync(0xffffffffu, j < c.RT && c.act[j]);
+        if ((m >> lane) & 1u) {
+          const int pos = w + __popc(m & ((1u << lane) - 1u));
+          if (pos < c.WS) c.wl[pos] = j;
+        }
+        w += __popc(m);
+      }
+      if (lane == 0) { *nw = w; ++((Hdr2*)smem_fast)->n_rounds; }
     }
     __syncthreads();
     const int w = *nw;
@@ -273,15 +302,27 @@ __device__ __noinline__ int schur_pdas2(int rounds) {
       }
       c.S[p] = s;
     }
-    if (threadIdx.x < w) c.rw[threadIdx.x] = res0[c.wl[threadIdx.x]];
+    if (threadIdx.x < w) {
+      c.rw[threadIdx.x] = res0[c.wl[threadIdx.x]];
+      c.rs[threadIdx.x] = c.S[TRI(threadIdx.x) + threadIdx.x];
+    }
+    if (threadIdx.x == 0) *sing = 0;
     __syncthreads();
-    if (warp == 0) {
+    // small working sets: one warp, right-looking in place (S <- L); larger ones: the blocked routine (S <- L^-1)
+    const bool blocked = w > 12;
+    if (blocked) {
+      chol_inverse_sh((int)(c.S - c.Gb), w, (int)(c.dlam - c.Gb), (int)(c.rs - c.Gb));
+    } else if (warp == 0) {
       const int sg = small_chol(c.S, w);
-      if (!sg) {
-        const double x = small_solve(c.S, w, lane < w ? c.rw[lane] : 0.0);
+      if (lane == 0) *sing = sg;
+    }
+    if (warp == 0) {
+      __syncwarp();
+      if (!*(volatile int*)sing) {
+        const double b = lane < w ? c.rw[lane] : 0.0;
+        const double x = blocked ? inv_solve(c.S, w, b) : small_solve(c.S, w, b);
         if (lane < w) c.lw[lane] = x;
       }
-      if (lane == 0) *sing = sg;
     }
     __syncthreads();
     if (*sing) return 3;
@@ -329,7 +370,8 @@ __device__ __noinline__ int schur_pdas2(int rounds) {
       v = block_max(v, c.red);
       if (v <= 0.1 * cert_tol || pass == 2) break;
       if (warp == 0) {
-        const double x = small_solve(c.S, w, lane < w ? c.res[c.wl[lane]] : 0.0);
+        const double b = lane < w ? c.res[c.wl[lane]] : 0.0;
+        const double x = blocked ? inv_solve(c.S, w, b) : small_solve(c.S, w, b);
         if (lane < w) c.lw[lane] += x;
       }
       __syncthreads();
@@ -344,7 +386,9 @@ __device__ __forceinline__ int solve_qp2(const Ctx2& c) {
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.act[j] = 0;
   __syncthreads();
   schur_prepare2();
-  const int rs = schur_pdas2(3 * c.hd->pdas_first);
+  // 3 pdas_first rounds of free updates, then at most 2 pdas_first one-change rounds: past that an interior-point solve
+  // (about 15 factorisations) is the cheaper way out
+  const int rs = schur_pdas2(3 * c.hd->pdas_first, 2 * c.hd->pdas_first);
   if (rs == 1) return DMPC_SOLVED;
   // singular S: the penalty rounds tolerate dependent rows.  Overflow / round cap: large or cycling working sets, for
   // which the penalty rounds almost never certify either (measured) - straight to the interior-point phase.

@@ -69,6 +69,7 @@ __device__ __forceinline__ int certify_update(const Ctx& c, const DevParams& P) 
   for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) {
     if (!row_valid(c, j)) continue;
     const double h = row_h(c, P, j);
+    if (!(fabs(c.res[j]) < 1e300) || !(fabs(c.lam[j]) < 1e300)) { changed = 1; continue; }  // NaN / inf never certifies
     if (!c.act[j]) {
       if (c.res[j] > P.cert_tol * (1.0 + fabs(h))) { c.act[j] = 1; changed = 1; }
     } else if (c.lam[j] < -P.cert_tol * lm) {
