@@ -42,7 +42,7 @@ extern "C" int dmpc_version(void) { return 100; }
 extern "C" void dmpc_default_options(dmpc_options* o) {
   if (!o) return;
   o->polish_delta = 1e-9; o->cert_tol = 1e-9; o->ipm_mu0 = 1e-6;
-  o->polish_refine = 4; o->pdas_first = 6; o->pdas_after = 4; o->ipm_max_iter = 60;
+  o->polish_refine = 4; o->pdas_first = 4; o->pdas_after = 2; o->ipm_max_iter = 60;
   o->engine = DMPC_ENGINE_AUTO; o->order_hint = 1;
 }
 

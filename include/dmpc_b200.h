@@ -55,8 +55,9 @@ typedef struct dmpc_options {
   double cert_tol;        /* relative KKT certificate tolerance, 1e-9                                  */
   double ipm_mu0;         /* first complementarity target of the interior-point phase, 1e-6            */
   int32_t polish_refine;  /* refinement steps per polish solve (OSQP's polish_refine_iter), 4         */
-  int32_t pdas_first;     /* active-set polish rounds tried before the interior-point phase, 6         */
-  int32_t pdas_after;     /* active-set polish rounds after each interior-point phase, 4               */
+  int32_t pdas_first;     /* active-set round budget before the interior-point phase, 4 (fast engine: 3x free Schur
+                             rounds + 2x one-change rounds; generic engine / singular S: that many penalty rounds)   */
+  int32_t pdas_after;     /* active-set polish rounds after each interior-point phase, 2               */
   int32_t ipm_max_iter;   /* interior-point iteration cap per phase, 60                                */
   int32_t engine;         /* 0 auto, 1 generic engine (any horizon, global spill), 2 fast engine (workspace packed in
                              shared memory; dmpc_create fails if the horizon does not fit)                     */
