@@ -372,91 +372,69 @@ __device__ __forceinline__ void build_K2(const Ctx2& c) {
   __syncthreads();
 }
 
-// In place: K (SPD, packed lower) -> L^-1 (packed lower), K = L L'.  Blocked, 8 columns per step, three barriers per
-// step instead of one per pivot.  Step s (rows/columns b0 = 8s .. b0+bs-1):
-//   A  warp 0 factorises the bs x bs diagonal block in registers (one row per lane, shuffles) and inverts it (one column
-//      per lane); its inverse replaces the block.  Meanwhile the other warps form T = L[blk, <b0] * Linv[<b0, <b0] (rows
-//      of L^-1 above the block are final, the block's own row of L is final since the previous step's panel) in c.Z.
-//   B  panel: L[i, blk] = K[i, blk] * Lss^-T for the rows below; and row block of the inverse: Linv[blk, <b0] = -Lss^-1 T.
-//   C  trailing update K[i][j] -= L[i, blk] . L[j, blk] in 2x2 register tiles.
+// In place: A (SPD, packed lower) -> L^-1 (packed lower), A = L L'.  Blocked, 8 columns per step, with look-ahead:
+// two barriers per step and the serial part (the 8 x 8 diagonal block) hidden behind the trailing update.
+// Step s (rows/columns b0 = 8s .. b0+bs-1), entered with the diagonal block already replaced by its inverse factor
+// Lss^-1 and T = L[blk, <b0] * Linv[<b0, <b0] in the scratch:
+//   B    panel L[i, blk] = A[i, blk] * Lss^-T for the rows below;  row block of the inverse Linv[blk, <b0] = -Lss^-1 T.
+//   C/A' warp 0 applies the panel to the NEXT diagonal block, factorises it in registers (one row per lane, shuffles)
+//        and inverts it (one column per lane); the other warps do the rest of the trailing update
+//        A[i][j] -= L[i, blk] . L[j, blk] in 2 x 2 register tiles and then the next step's T.
 // Non-positive pivots are floored.  With d0 (the diagonal before the factorisation) a pivot below 1e-11 of its original
 // diagonal entry sets *sing (numerically dependent rows); the factorisation still runs to the end.
 // A: packed lower n x n (any n >= 1), T: 8 x n scratch, tri: the (i << 8 | j) table of packed-lower indices.
+__device__ __forceinline__ void chol_diag_block(double* A, const int b0, const int bs, const double* d0, int* sing) {
+  const int lane = threadIdx.x & 31;
+  const unsigned full = 0xffffffffu;
+  const bool own = lane < bs;
+  const double* row = A + TRI(b0 + (own ? lane : 0)) + b0;
+  double a[8], rsv[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) a[q] = (own && q <= lane) ? row[q] : (q == lane ? 1.0 : 0.0);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    double d = __shfl_sync(full, a[k], k);
+    if (d0 && k < bs && lane == 0 && !(d > 1e-11 * d0[b0 + k])) *sing = 1;
+    if (!(d > 1e-300)) d = 1e-30;
+    const double rk = rsqrt(d);
+    rsv[k] = rk;
+    const double lk = (lane == k) ? d * rk : a[k] * rk;
+#pragma unroll
+    for (int j = k + 1; j < 8; ++j) {
+      const double v = __shfl_sync(full, lk, j);
+      a[j] = fma(-lk, v, a[j]);
+    }
+    a[k] = lk;
+  }
+  // column `lane` of the inverse: x[i] = -(sum_{m<i} l_im x[m]) / l_ii, x[lane] = 1 / l_ll, zero above
+  double x[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    double sacc = 0.0;
+#pragma unroll
+    for (int m = 0; m < i; ++m) {
+      const double v = __shfl_sync(full, a[m], i);
+      sacc = fma(v, x[m], sacc);
+    }
+    x[i] = (i == lane) ? rsv[i] : (i > lane ? -sacc * rsv[i] : 0.0);
+  }
+  if (own) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i >= lane && i < bs) A[TRI(b0 + i) + b0 + lane] = x[i];
+  }
+}
+
 __device__ __forceinline__ void chol_inverse_blk(double* A, const int n, double* T, const unsigned short* tri,
                                                  const double* d0, int* sing) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const unsigned full = 0xffffffffu;
   const int ldt = n;
+  if (n <= 0) return;
+  if (warp == 0) chol_diag_block(A, 0, min(8, n), d0, sing);
+  __syncthreads();
 #pragma unroll 1
   for (int b0 = 0; b0 < n; b0 += 8) {
     const int bs = min(8, n - b0);
-    // ---------------- A
-    if (warp == 0) {
-      const bool own = lane < bs;
-      const double* row = A + TRI(b0 + (own ? lane : 0)) + b0;
-      double a[8], rsv[8];
-#pragma unroll
-      for (int q = 0; q < 8; ++q) a[q] = (own && q <= lane) ? row[q] : (q == lane ? 1.0 : 0.0);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        double d = __shfl_sync(full, a[k], k);
-        if (d0 && k < bs && lane == 0 && !(d > 1e-11 * d0[b0 + k])) *sing = 1;
-        if (!(d > 1e-300)) d = 1e-30;
-        const double rk = rsqrt(d);
-        rsv[k] = rk;
-        const double lk = (lane == k) ? d * rk : a[k] * rk;
-#pragma unroll
-        for (int j = k + 1; j < 8; ++j) {
-          const double v = __shfl_sync(full, lk, j);
-          a[j] = fma(-lk, v, a[j]);
-        }
-        a[k] = lk;
-      }
-      // column `lane` of the inverse: x[i] = -(sum_{m<i} l_im x[m]) / l_ii, x[lane] = 1 / l_ll, zero above
-      double x[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        double sacc = 0.0;
-#pragma unroll
-        for (int m = 0; m < i; ++m) {
-          const double v = __shfl_sync(full, a[m], i);
-          sacc = fma(v, x[m], sacc);
-        }
-        x[i] = (i == lane) ? rsv[i] : (i > lane ? -sacc * rsv[i] : 0.0);
-      }
-      if (own) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-          if (i >= lane && i < bs) A[TRI(b0 + i) + b0 + lane] = x[i];
-      }
-    } else if (b0 > 0) {
-      // T[r][j] = sum_{k=j}^{b0-1} L[b0+r][k] Linv[k][j]; an item = (column j, half of the block's rows)
-#pragma unroll 1
-      for (int e = threadIdx.x - 32; e < 2 * b0; e += QP_THREADS - 32) {
-        const int j = e >> 1, rh = (e & 1) * 4;
-        if (rh >= bs) continue;
-        const double* l0 = A + TRI(b0 + rh);  // rows past the block (bs < 8) repeat its last row; never stored
-        const double* l1 = A + TRI(b0 + min(rh + 1, bs - 1));
-        const double* l2 = A + TRI(b0 + min(rh + 2, bs - 1));
-        const double* l3 = A + TRI(b0 + min(rh + 3, bs - 1));
-        double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
-        int tk = TRI(j) + j;
-#pragma unroll 2
-        for (int k = j; k < b0; ++k) {
-          const double v = A[tk];
-          tk += k + 1;
-          t0 = fma(l0[k], v, t0);
-          t1 = fma(l1[k], v, t1);
-          t2 = fma(l2[k], v, t2);
-          t3 = fma(l3[k], v, t3);
-        }
-        if (rh < bs) T[(rh + 0) * ldt + j] = t0;
-        if (rh + 1 < bs) T[(rh + 1) * ldt + j] = t1;
-        if (rh + 2 < bs) T[(rh + 2) * ldt + j] = t2;
-        if (rh + 3 < bs) T[(rh + 3) * ldt + j] = t3;
-      }
-    }
-    __syncthreads();
     // ---------------- B
     {
       const int mrows = n - b0 - bs;
@@ -473,7 +451,7 @@ __device__ __forceinline__ void chol_inverse_blk(double* A, const int n, double*
         for (int q = 0; q < 8; ++q) kv[q] = (pan && q < bs && q <= cp + 1) ? kr[q] : 0.0;
         __syncwarp();  // in place: every thread of the row has read before any of them writes
         if (pan) {
-          // L[i][b0+cc] = sum_{m<=cc} K[i][b0+m] Li[cc][m]
+          // L[i][b0+cc] = sum_{m<=cc} A[i][b0+m] Li[cc][m]
           if (cp < bs) {
             const double* li0 = A + TRI(b0 + cp) + b0;
             double o0 = 0.0;
@@ -507,12 +485,31 @@ __device__ __forceinline__ void chol_inverse_blk(double* A, const int n, double*
       }
     }
     __syncthreads();
-    // ---------------- C
-    const int m2 = (n - b0 - bs + 1) >> 1;  // 2 x 2 tiles of the trailing block (the last one is 1 row short for odd sizes)
-    if (m2 > 0) {
-      const int base = b0 + bs, ntl = (m2 * (m2 + 1)) >> 1;
+    // ---------------- C / A'
+    const int base = b0 + bs, rem = n - base;
+    if (rem <= 0) break;
+    const int nbs = min(8, rem);                 // next diagonal block
+    const int m2 = (rem + 1) >> 1;               // 2 x 2 tiles of the trailing block (last one a row short for odd sizes)
+    const int ntl = (m2 * (m2 + 1)) >> 1;
+    const int ndiag = rem <= 8 ? ntl : 10;       // tiles inside the next diagonal block (the first 4 tile rows)
+    if (warp == 0) {
+      // the next diagonal block, element per lane, then factorise / invert it
+      const int nel = (nbs * (nbs + 1)) >> 1;
 #pragma unroll 1
-      for (int e = threadIdx.x; e < ntl; e += QP_THREADS) {
+      for (int e = lane; e < nel; e += 32) {
+        const int ij = tri[e], i = base + (ij >> 8), j = base + (ij & 255);
+        const double* li = A + TRI(i) + b0;
+        const double* lj = A + TRI(j) + b0;
+        double sacc = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) if (q < bs) sacc = fma(li[q], lj[q], sacc);
+        A[TRI(i) + j] -= sacc;
+      }
+      __syncwarp();
+      chol_diag_block(A, base, nbs, d0, sing);
+    } else {
+#pragma unroll 1
+      for (int e = ndiag + (int)threadIdx.x - 32; e < ntl; e += QP_THREADS - 32) {
         const int ij = tri[e], i = base + 2 * (ij >> 8), j = base + 2 * (ij & 255);
         const bool i1 = i + 1 < n;
         const double* li0 = A + TRI(i) + b0;
@@ -537,8 +534,33 @@ __device__ __forceinline__ void chol_inverse_blk(double* A, const int n, double*
           k1[1] -= s11;
         }
       }
-      __syncthreads();
+      // next step's T[r][j] = sum_{k=j}^{base-1} L[base+r][k] Linv[k][j]; an item = (column j, half of the block's rows)
+#pragma unroll 1
+      for (int e = threadIdx.x - 32; e < 2 * base; e += QP_THREADS - 32) {
+        const int j = e >> 1, rh = (e & 1) * 4;
+        if (rh >= nbs) continue;
+        const double* l0 = A + TRI(base + rh);  // rows past the block (nbs < 8) repeat its last row; never stored
+        const double* l1 = A + TRI(base + min(rh + 1, nbs - 1));
+        const double* l2 = A + TRI(base + min(rh + 2, nbs - 1));
+        const double* l3 = A + TRI(base + min(rh + 3, nbs - 1));
+        double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+        int tk = TRI(j) + j;
+#pragma unroll 2
+        for (int k = j; k < base; ++k) {
+          const double v = A[tk];
+          tk += k + 1;
+          t0 = fma(l0[k], v, t0);
+          t1 = fma(l1[k], v, t1);
+          t2 = fma(l2[k], v, t2);
+          t3 = fma(l3[k], v, t3);
+        }
+        if (rh < nbs) T[(rh + 0) * ldt + j] = t0;
+        if (rh + 1 < nbs) T[(rh + 1) * ldt + j] = t1;
+        if (rh + 2 < nbs) T[(rh + 2) * ldt + j] = t2;
+        if (rh + 3 < nbs) T[(rh + 3) * ldt + j] = t3;
+      }
     }
+    __syncthreads();
   }
 }
 
