@@ -98,6 +98,8 @@ def make_params(Q, Qs, R, dR, N, dt, map_obj, wq=0.0, model_param=None, sys_lim=
 
 
 def default_lib_path():
+    if os.environ.get("DMPC_B200_LIB"):  # development: A/B of two builds of the same C ABI in one GPU session
+        return os.environ["DMPC_B200_LIB"]
     return os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libdmpc_b200.so")
 
 

@@ -168,10 +168,15 @@ __device__ __forceinline__ void stage_outputs2(const Ctx2& c, const double* uv, 
   for (int w = threadIdx.x; w < 4 * c.N; w += QP_THREADS) {
     const int t = w >> 2, q = w & 3;
     const double* g = &GB(c, t, q, 0);
-    double s0 = with_offset ? c.cr[t * c.NR + q] : 0.0, s1 = 0.0;
+    double s0 = with_offset ? c.cr[t * c.NR + q] : 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
     const int jn = 2 * (t + 1);
-    for (int j = 0; j < jn; j += 2) { s0 = fma(g[j], uv[j], s0); s1 = fma(g[j + 1], uv[j + 1], s1); }
-    o[w] = s0 + s1;
+    int j = 0;
+    for (; j + 3 < jn; j += 4) {
+      s0 = fma(g[j], uv[j], s0); s1 = fma(g[j + 1], uv[j + 1], s1);
+      s2 = fma(g[j + 2], uv[j + 2], s2); s3 = fma(g[j + 3], uv[j + 3], s3);
+    }
+    if (j < jn) { s0 = fma(g[j], uv[j], s0); s1 = fma(g[j + 1], uv[j + 1], s1); }
+    o[w] = (s0 + s1) + (s2 + s3);
   }
 }
 
@@ -195,33 +200,43 @@ __device__ __forceinline__ void rows_to_stage2(const Ctx2& c, const double* w, d
 }
 
 // out[j] = base[j]*bs + ws * (sum_t Gb_t[:,j]' wo_t + box(wbox)).  `sparse`: wo is zero outside the active stages.
+// Two threads per column (even / odd positions of the stage walk), combined by one shuffle.
 __device__ __forceinline__ void apply_Gt2(const Ctx2& c, const double* wo, const double* wbox, double ws,
                                           const double* base, double bs, double* out, bool sparse) {
+  const int items = 2 * c.nu;
 #pragma unroll 1
-  for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) {
-    double s0 = 0.0, s1 = 0.0;
-    if (sparse) {
-      const int nas = *c.nas;
-      for (int a = 0; a < nas; ++a) {
-        const int t = c.asl[a];
-        if (2 * (t + 1) <= j) continue;
-        const double* w4 = wo + 4 * t;
-        s0 = fma(GB(c, t, 0, j), w4[0], s0); s1 = fma(GB(c, t, 1, j), w4[1], s1);
-        s0 = fma(GB(c, t, 2, j), w4[2], s0); s1 = fma(GB(c, t, 3, j), w4[3], s1);
-      }
-    } else {
-      for (int t = j >> 1; t < c.N; ++t) {
-        const double* w4 = wo + 4 * t;
-        s0 = fma(GB(c, t, 0, j), w4[0], s0); s1 = fma(GB(c, t, 1, j), w4[1], s1);
-        s0 = fma(GB(c, t, 2, j), w4[2], s0); s1 = fma(GB(c, t, 3, j), w4[3], s1);
+  for (int e0 = 0; e0 < items; e0 += QP_THREADS) {  // uniform trip count: the shuffle below needs whole warps
+    const int e = e0 + threadIdx.x;
+    const bool valid = e < items;
+    const int j = valid ? e >> 1 : 0, half = e & 1;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    if (valid) {
+      if (sparse) {
+        const int nas = *c.nas;
+        for (int a = half; a < nas; a += 2) {
+          const int t = c.asl[a];
+          if (2 * (t + 1) <= j) continue;
+          const double* w4 = wo + 4 * t;
+          s0 = fma(GB(c, t, 0, j), w4[0], s0); s1 = fma(GB(c, t, 1, j), w4[1], s1);
+          s2 = fma(GB(c, t, 2, j), w4[2], s2); s3 = fma(GB(c, t, 3, j), w4[3], s3);
+        }
+      } else {
+        for (int t = (j >> 1) + half; t < c.N; t += 2) {
+          const double* w4 = wo + 4 * t;
+          s0 = fma(GB(c, t, 0, j), w4[0], s0); s1 = fma(GB(c, t, 1, j), w4[1], s1);
+          s2 = fma(GB(c, t, 2, j), w4[2], s2); s3 = fma(GB(c, t, 3, j), w4[3], s3);
+        }
       }
     }
-    double s = s0 + s1;
-    if (wbox) {
-      const double* wb = wbox + 4 * (j >> 1) + 2 * (j & 1);
-      s += wb[0] - wb[1];
+    double s = (s0 + s1) + (s2 + s3);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    if (valid && half == 0) {
+      if (wbox) {
+        const double* wb = wbox + 4 * (j >> 1) + 2 * (j & 1);
+        s += wb[0] - wb[1];
+      }
+      out[j] = (base ? bs * base[j] : 0.0) + ws * s;
     }
-    out[j] = (base ? bs * base[j] : 0.0) + ws * s;
   }
 }
 
@@ -229,13 +244,14 @@ __device__ __forceinline__ void apply_Gt2(const Ctx2& c, const double* wo, const
 __device__ __forceinline__ void apply_H2(const Ctx2& c, const double* uv, double* out) {
 #pragma unroll 1
   for (int i = threadIdx.x; i < c.nu; i += QP_THREADS) {
-    double s0 = 0.0, s1 = 0.0;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
     const double* hr = c.H + TRI(i);
     int j = 0;
     for (; j + 1 <= i; j += 2) { s0 = fma(hr[j], uv[j], s0); s1 = fma(hr[j + 1], uv[j + 1], s1); }
     for (; j <= i; ++j) s0 = fma(hr[j], uv[j], s0);
-    for (j = i + 1; j < c.nu; ++j) s1 = fma(c.H[TRI(j) + i], uv[j], s1);
-    out[i] = s0 + s1;
+    for (j = i + 1; j + 1 < c.nu; j += 2) { s2 = fma(c.H[TRI(j) + i], uv[j], s2); s3 = fma(c.H[TRI(j + 1) + i], uv[j + 1], s3); }
+    if (j < c.nu) s2 = fma(c.H[TRI(j) + i], uv[j], s2);
+    out[i] = (s0 + s1) + (s2 + s3);
   }
 }
 
