@@ -20,6 +20,9 @@ struct dmpc_handle {
   double* d_gws;
   int *d_cost, *d_order;  // fast engine: per-QP cost of the last call and the launch order derived from it
   int order_B;            // batch size d_order is valid for (0: none yet)
+  int nsm;                // SMs of the device
+  size_t smem_alone;      // dynamic shared memory request that keeps a CTA alone on its SM
+  cudaStream_t host_stream;  // dmpc_solve_batch_host
   // staging for the host-buffer entry point
   char* d_stage;
   size_t stage_bytes;
@@ -151,8 +154,16 @@ extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_
     if (fits && h->opt.engine != DMPC_ENGINE_GENERIC) {
       h->fast = 1; h->smem_bytes = sb2; h->gws_stride = 0;
       CUDA_TRY(h, cudaMalloc(&h->d_cost, sizeof(int) * (size_t)max_batch));
-      CUDA_TRY(h, cudaMalloc(&h->d_order, sizeof(int) * (size_t)max_batch));
-      CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb2));
+      CUDA_TRY(h, cudaMalloc(&h->d_order, sizeof(int) * ((size_t)max_batch + 1)));  // [max_batch]: expensive-QP count
+      {
+        CUDA_TRY(h, cudaDeviceGetAttribute(&h->nsm, cudaDevAttrMultiProcessorCount, device));
+        // alone on the SM: a second CTA of this kernel (sb2 + 1 KB system share each) must not fit beside it
+        const size_t per_sm = (size_t)optin + 1024;
+        h->smem_alone = per_sm > 2 * (sb2 + 1024) ? per_sm - (sb2 + 1024) - 1024 + 16 : sb2;
+        if (h->smem_alone > (size_t)optin) h->smem_alone = (size_t)optin;
+        if (h->smem_alone < sb2) h->smem_alone = sb2;
+        CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_alone));
+      }
       return DMPC_OK;
     }
   }
@@ -175,6 +186,7 @@ extern "C" void dmpc_destroy(dmpc_handle* h) {
   if (h->d_gws) cudaFree(h->d_gws);
   if (h->d_cost) cudaFree(h->d_cost);
   if (h->d_order) cudaFree(h->d_order);
+  if (h->host_stream) cudaStreamDestroy(h->host_stream);
   if (h->d_stage) cudaFree(h->d_stage);
   delete h;
 }
@@ -214,10 +226,33 @@ extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* s
     // call of the same batch size spent on them - consecutive MPC steps of a scenario are alike, so the few
     // interior-point QPs start first instead of becoming the tail of the grid.  Scheduling only; results do not change.
     const bool hint = h->opt.order_hint != 0;
+    bp.nhard = nullptr; bp.part = 0;
     if (hint) { bp.cost = h->d_cost; if (h->order_B == io->B) bp.order = h->d_order; }
-    lpv_qp_fast_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+    if (bp.order && h->smem_alone > h->smem_bytes) {
+      // The QPs that needed the interior-point phase last time (order[0 .. nhard), ~1 %, ~1.6 ms each alone but 2.2 ms
+      // when two other CTAs share the SM) are launched first with a shared-memory request that keeps each of them alone
+      // on an SM; the bulk follows in the same stream as a programmatic dependent launch: it may start as soon as every
+      // CTA of the first part is resident (they signal at entry), so it fills the other SMs and never has to be waited
+      // for by a CTA that needs a whole SM.  Same kernel, same arithmetic per QP.
+      cudaStream_t st = (cudaStream_t)stream;
+      bp.nhard = h->d_order + h->max_batch;
+      bp.part = 1;
+      lpv_qp_fast_kernel<<<io->B < h->nsm ? io->B : h->nsm, QP_THREADS, h->smem_alone, st>>>(h->P, bp);
+      bp.part = 2;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)io->B); cfg.blockDim = dim3(QP_THREADS);
+      cfg.dynamicSmemBytes = h->smem_bytes; cfg.stream = st;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      CUDA_TRY(h, cudaLaunchKernelEx(&cfg, lpv_qp_fast_kernel, h->P, bp));
+      h->launches++;
+    } else {
+      lpv_qp_fast_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+    }
     if (hint) {
-      order_by_cost_kernel<<<1, ORDER_THREADS, 0, (cudaStream_t)stream>>>(h->d_cost, h->d_order, io->B);
+      order_by_cost_kernel<<<1, ORDER_THREADS, 0, (cudaStream_t)stream>>>(h->d_cost, h->d_order, h->d_order + h->max_batch, io->B, h->nsm);
       h->order_B = io->B;
       h->launches++;
     }
@@ -253,7 +288,8 @@ extern "C" int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io) {
   }
   if (rows > N + 1) return fail(h, DMPC_ERR_ARG, "Last_xPredicted has more than N+1 rows%s");
   char* d = h->d_stage;
-  cudaStream_t s = 0;
+  if (!h->host_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->host_stream, cudaStreamNonBlocking));
+  cudaStream_t s = h->host_stream;  // the call is synchronous and touches host buffers only: a private stream
 #define H2D(dst_off, src, bytes) do { if (src) CUDA_TRY(h, cudaMemcpyAsync(d + (dst_off), (src), (bytes), cudaMemcpyHostToDevice, s)); } while (0)
 #define D2H(dst, src_off, bytes) do { if (dst) CUDA_TRY(h, cudaMemcpyAsync((dst), d + (src_off), (bytes), cudaMemcpyDeviceToHost, s)); } while (0)
   H2D(o_x0, io->x0, (size_t)B * 9 * 8); H2D(o_xp, io->xprev, (size_t)B * rows * 9 * 8); H2D(o_up, io->uprev, (size_t)B * N * 2 * 8);

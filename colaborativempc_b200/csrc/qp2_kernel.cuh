@@ -120,7 +120,17 @@ __device__ __forceinline__ void rollout2(const Ctx2& c, const double* x0, double
 }
 
 __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid_constant__ DevParams P, const BatchPtrs io) {
+  if (io.part == 1) asm volatile("griddepcontrol.launch_dependents;");  // split launch: the bulk may be scheduled now
   if (blockIdx.x >= io.B) return;
+  if (io.part) {
+    const int nh = *io.nhard;  // <= number of SMs = part 1's grid (order_by_cost_kernel clamps it)
+    if (io.part == 1 ? (int)blockIdx.x >= nh : (int)blockIdx.x < nh) {
+      // part 2 shares no data with part 1, but whatever follows in the stream needs both: one idle CTA of part 2 stays
+      // until part 1 has completed and flushed, so that "part 2 complete" implies "part 1 complete"
+      if (io.part == 2 && blockIdx.x == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
+      return;
+    }
+  }
   const int b = io.order ? io.order[blockIdx.x] : blockIdx.x;
   const int N = P.N, nn = P.nn;
   if (threadIdx.x == 0) {
@@ -295,7 +305,8 @@ __device__ __forceinline__ int cost_class(int cst) {
   return cst >= 24 * 16 ? 7 : cst >= 24 ? 6 : cst >= 12 ? 5 : cst >= 6 ? 4 : cst >= 4 ? 3 : cst >= 3 ? 2 : cst >= 2 ? 1 : 0;
 }
 
-__global__ void __launch_bounds__(ORDER_THREADS, 1) order_by_cost_kernel(const int* __restrict__ cost, int* __restrict__ order, int B) {
+__global__ void __launch_bounds__(ORDER_THREADS, 1) order_by_cost_kernel(const int* __restrict__ cost, int* __restrict__ order,
+                                                                         int* __restrict__ nhard, int B, int nsm) {
   __shared__ int wsum[ORDER_THREADS / 32];
   __shared__ int base;
   const int chunk = (B + ORDER_THREADS - 1) / ORDER_THREADS;
@@ -330,7 +341,10 @@ __global__ void __launch_bounds__(ORDER_THREADS, 1) order_by_cost_kernel(const i
       if (cost_class(cost[i]) == cls) order[pos++] = i;
     const int total = wsum[ORDER_THREADS / 32 - 1];
     __syncthreads();
-    if (threadIdx.x == 0) base += total;
+    if (threadIdx.x == 0) {
+      base += total;
+      if (cls == 6) *nhard = min(base, nsm);  // classes 7 and 6: at least one interior-point iteration
+    }
     __syncthreads();
   }
 }

@@ -47,6 +47,10 @@ struct BatchPtrs {
   // need the interior-point phase do not start at the end of the grid and become the tail of the launch
   const int* order;
   int* cost;
+  // split launch: order[0 .. *nhard) are the QPs that needed the interior-point phase last time; part 1 (side stream,
+  // one CTA per SM) solves exactly those, part 2 (main launch) skips them; part 0: one launch does everything
+  const int* nhard;
+  int part;
 };
 
 // ---------------------------------------------------------------------------------------------------

@@ -82,3 +82,8 @@ ok = o["status"] == 1
 err = np.abs(g["z"] - o["z"]).max(1) / (1 + np.abs(o["z"]).max(1))
 print("oracle certified %d of %d; rel err z vs oracle: max %.2e (over certified), obj rel %.2e" % (
     ok.sum(), sel.size, err[ok].max() if ok.any() else -1, (np.abs(g["obj"] - o["obj"]) / (1 + np.abs(o["obj"])))[ok].max() if ok.any() else -1))
+
+# ---- what bounds the batch: the same batch without its interior-point QPs / without the long-round QPs
+timeit(it == 0, "batch minus ipm QPs (replicated to 4096)")
+timeit((it == 0) & (pv < 12), "batch minus ipm and rounds>=12")
+timeit((it == 0) & (pv < 6), "batch minus ipm and rounds>=6")
