@@ -112,7 +112,7 @@ __device__ __forceinline__ int block_argmax(const Ctx2& c, double v, int idx, do
 //                slots, else the most violated ones;
 //   safe mode (after a repeated working set): one change per round - drop the most negative multiplier, else add the
 //                most violated row.
-__device__ __forceinline__ int schur_update(const Ctx2& c, int safe) {
+__device__ __forceinline__ int schur_update(const Ctx2& c, int safe, int first) {
   const double cert_tol = c.hd->cert_tol;
   double lm = 0.0;
 #pragma unroll 1
@@ -137,6 +137,9 @@ __device__ __forceinline__ int schur_update(const Ctx2& c, int safe) {
   const int nviol = (int)(total & 4095), nneg = (int)((total >> 12) & 4095), nkeep = (int)((total >> 24) & 4095);
   if ((total >> 36) != 0) return 2;  // non-finite iterate: leave the rounds
   if (nviol == 0 && nneg == 0) return 1;
+  // far more rows violated at the unconstrained optimum than the working set can hold: the rounds would end in overflow
+  // (measured: of the QPs with more than 1.5 WS violated rows at u0, 95 % do) - do not spend them
+  if (first && 2 * nviol > 3 * c.WS) return 2;
   if (!safe) {
     const int room = c.WS - nkeep;
     if (nviol <= room) {
@@ -219,7 +222,7 @@ __device__ __noinline__ int schur_pdas2(int rounds, int safe_rounds) {
 #pragma unroll 1
   for (int r = 0; r < rounds + safe_rounds; ++r) {
     {
-      const int st = schur_update(c, safe);
+      const int st = schur_update(c, safe, r == 0);
       if (st) return st;
     }
     if (!safe) {
