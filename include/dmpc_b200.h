@@ -61,9 +61,10 @@ typedef struct dmpc_options {
   int32_t ipm_max_iter;   /* interior-point iteration cap per phase, 60                                */
   int32_t engine;         /* 0 auto, 1 generic engine (any horizon, global spill), 2 fast engine (workspace packed in
                              shared memory; dmpc_create fails if the horizon does not fit)                     */
-  int32_t order_hint;     /* fast engine: 1 = a call starts its QPs in decreasing order of what the previous call of the
-                             same batch size spent on each (consecutive MPC steps are alike; scheduling only, the
-                             results are independent of it; calls on one handle must then be stream-ordered), 0 = off */
+  int32_t order_hint;     /* fast engine: 1 = a call orders and splits its launch by what the previous call of the same
+                             batch size spent on each QP index (most expensive first, the interior-point ones alone on
+                             an SM; consecutive MPC steps are alike).  Scheduling only: results are independent of it.
+                             Calls on one handle must then be stream-ordered with each other.  0 = off               */
 } dmpc_options;
 
 /* Per-QP status values mirror OSQP's status_val so `feasible` is derived as LPV_Planner.py:246-248. */
