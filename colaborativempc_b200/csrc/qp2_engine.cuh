@@ -24,7 +24,7 @@
 struct Hdr2 {
   int N, nn, NR, cnt;
   int refine, pdas_first, pdas_after, ipm_max;
-  int n_rounds, n_ipm, pad0, pad1;
+  int n_rounds, n_ipm, WS, pad1;  // WS: working-set capacity of the Schur rounds (found once by the first carve)
   double delta, cert_tol, ipm_mu0;
   double Qs[9];
   double Qsi[9];  // (2 Qs)^-1, for the exact slack elimination of the Schur-complement rounds
@@ -61,7 +61,7 @@ struct Ctx2 {
 // extra (cost-only) rows r >= 4, same packing per row: row r-4 occupies N(N+1) doubles
 #define GX(c, t, r, j) (c).Gx[((r) - 4) * (c).N * ((c).N + 1) + (t) * ((t) + 1) + (j)]
 
-__host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int nn, int NR) {
+__host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int nn, int NR, int ws_known = 0) {
   c.N = N; c.nn = nn; c.nu = 2 * N; c.NR = NR;
   c.rst = 4 + nn; c.Rs = N * c.rst; c.RT = c.Rs + 4 * N; c.ntri = N * (2 * N + 1);
   double* p = (double*)sm;
@@ -74,8 +74,8 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   c.Acol = take(27 * N); c.Bcol = take(4 * N);
   {  // Schur-round scratch aliases K + the linearisation block: largest working set (<= 32 rows) that fits
     const size_t room = (size_t)((c.Acol + 31 * N) - c.K);
-    int ws = 32;
-    while (ws > 1 && ((size_t)c.nu * (ws + 1) + (size_t)ws * (ws + 1) / 2 > room || 8 * ws > 2 * c.RT)) --ws;  // 8 x ws
+    int ws = ws_known > 0 ? ws_known : 32;
+    while (ws_known <= 0 && ws > 1 && ((size_t)c.nu * (ws + 1) + (size_t)ws * (ws + 1) / 2 > room || 8 * ws > 2 * c.RT)) --ws;  // 8 x ws
     // scratch of the S factorisation lives in dlam/dtt
     c.WS = ws; c.ldy = ws + 1;
     c.Y = c.K; c.S = c.K + (size_t)c.nu * c.ldy;
@@ -116,7 +116,7 @@ __host__ __device__ inline size_t carve_workspace2(Ctx2& c, char* sm, int N, int
   Ctx2 c;                                                                        \
   {                                                                              \
     const Hdr2* hd_ = (const Hdr2*)smem_fast;                                    \
-    carve_workspace2(c, smem_fast + FAST_HDR_BYTES, hd_->N, hd_->nn, hd_->NR);   \
+    carve_workspace2(c, smem_fast + FAST_HDR_BYTES, hd_->N, hd_->nn, hd_->NR, hd_->WS);   \
     c.cnt = hd_->cnt; c.hd = hd_;                                                \
   }
 

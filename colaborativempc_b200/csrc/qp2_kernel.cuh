@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
     hd->N = N; hd->nn = nn; hd->NR = P.nrows; hd->cnt = cnt < 0 ? 0 : (cnt > nn ? nn : cnt);
     hd->refine = P.refine; hd->pdas_first = P.pdas_first; hd->pdas_after = P.pdas_after; hd->ipm_max = P.ipm_max;
     hd->n_rounds = 0; hd->n_ipm = 0;
+    { Ctx2 c0; carve_workspace2(c0, nullptr, N, nn, P.nrows); hd->WS = c0.WS; }
     hd->delta = P.delta; hd->cert_tol = P.cert_tol; hd->ipm_mu0 = P.ipm_mu0;
     for (int i = 0; i < 9; ++i) hd->Qs[i] = P.Qs[i];
     {  // (2 Qs)^-1 by cofactors (Qs symmetric positive definite, checked in dmpc_create)
