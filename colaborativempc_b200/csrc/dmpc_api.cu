@@ -8,6 +8,7 @@
 
 #include "qp_kernel.cuh"
 #include "qp2_kernel.cuh"
+#include "lpv_sim.cuh"
 
 struct dmpc_handle {
   dmpc_params params;
@@ -23,6 +24,7 @@ struct dmpc_handle {
   int nsm;                // SMs of the device
   size_t smem_alone;      // dynamic shared memory request that keeps a CTA alone on its SM
   cudaStream_t host_stream;  // dmpc_solve_batch_host
+  int sim_attr;              // lpv_sim_kernel's shared-memory opt-in done (long horizons)
   // staging for the host-buffer entry point
   char* d_stage;
   size_t stage_bytes;
@@ -335,6 +337,21 @@ __global__ void shift_pack_kernel(int B, int N, const double* __restrict__ z, do
       if (q < 2 && uold) uold[(size_t)b * 2 + q] = v;                               // OldSteering / OldAccelera
     }
   }
+}
+
+extern "C" int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, const double* d_u, double* d_out,
+                              int32_t* d_status, void* stream) {
+  if (!h || B < 0 || (B > 0 && (!d_xpred || !d_u || !d_out))) return DMPC_ERR_ARG;
+  if (B == 0) return DMPC_OK;
+  const size_t smem = (size_t)SIM_WARPS * h->P.N * 31 * sizeof(double);
+  if (smem > 48 * 1024 && !h->sim_attr) {
+    CUDA_TRY(h, cudaFuncSetAttribute(lpv_sim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    h->sim_attr = 1;
+  }
+  lpv_sim_kernel<<<(B + SIM_WARPS - 1) / SIM_WARPS, 32 * SIM_WARPS, smem, (cudaStream_t)stream>>>(h->P, B, d_xpred, d_u, d_out, d_status);
+  h->launches++;
+  CUDA_TRY(h, cudaGetLastError());
+  return DMPC_OK;
 }
 
 extern "C" int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, double* d_x0, double* d_xprev, double* d_uprev,

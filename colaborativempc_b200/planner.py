@@ -158,6 +158,22 @@ class BatchedPlannerLPV(object):
                                                     p(nbr_xy), p(pose), C.c_void_p(s.cuda_stream)))
 
 
+    def sim_batch(self, xpred, u, out=None, status=None, stream=None):
+        """Batched LPV_Model.sim (LPV_val.py:77-94) on device tensors: xpred [B,N+1,9], u [B,N,2] -> [B,N+1,9], status [B]."""
+        torch = _torch()
+        B = xpred.shape[0]
+        assert xpred.is_cuda and xpred.dtype == torch.float64 and xpred.is_contiguous() and tuple(xpred.shape) == (B, self.N + 1, 9)
+        assert u.is_cuda and u.dtype == torch.float64 and u.is_contiguous() and tuple(u.shape) == (B, self.N, 2)
+        if out is None:
+            out = torch.empty_like(xpred)
+        if status is None:
+            status = torch.empty((B,), dtype=torch.int32, device=xpred.device)
+        s = torch.cuda.current_stream(self.device) if stream is None else stream
+        self._check(self.lib.dmpc_sim_batch(self._h, B, xpred.data_ptr(), u.data_ptr(), out.data_ptr(), status.data_ptr(),
+                                            C.c_void_p(s.cuda_stream)))
+        return out, status
+
+
 def unpack_solution(z, N):
     """Views of res.x as PlannerLPV.solve unpacks it (LPV_Planner.py:162-180), incl. the duPred indexing of :175."""
     z = np.asarray(z)
@@ -237,3 +253,39 @@ class PlannerLPV(object):
         self.OldSteering = [self.uPred[0, 0]]
         self.OldAccelera = [self.uPred[0, 1]]
         return feasible, Solution, self.planes
+
+
+class LPV_Model(object):
+    """Drop-in for plan_lib.distributedPlanner.LPV_Model (LPV_val.py:7-94): same constructor, `xPred` attribute and
+    `sim(u)`; the roll-out runs in `lpv_sim_kernel` (a batch of one; `BatchedPlannerLPV.sim_batch` is the batched form)."""
+
+    # LPV_val.py:27-35,45-53: this class has its own defaults, different from PlannerLPV's
+    _MODEL = dict(lf=0.125, lr=0.125, m=1.98, I=0.06, Cf=60.0, Cr=60.0, mu=0.05)
+    _LIMITS = dict(vx_ref=4.5, max_vel=5, min_vel=0.2, max_rs=0.45, max_ls=0.45, max_ac=4.0, max_dc=3.0, sm=0.9)
+
+    def __init__(self, N, dt, map, model_param=None, sys_lim=None):
+        self.n_s, self.slack, self.n_u = 9, 3, 2
+        self.xPred = np.ones((N + 1, self.n_s))
+        self.dt, self.map, self.N = dt, map, N
+        self.first_it = True
+        self.OldSteering = [0.0]
+        self.OldAccelera = [0.0]
+        mp = dict(self._MODEL if model_param is None else model_param)
+        sl = dict(_abi.DEFAULT_LIMITS)
+        sl.update(self._LIMITS if sys_lim is None else sys_lim)
+        for k in ("lf", "lr", "m", "I", "Cf", "Cr", "mu"):
+            setattr(self, k, mp[k])
+        for k in ("vx_ref", "max_vel", "min_vel", "max_rs", "max_ls", "max_ac", "max_dc", "sm"):
+            setattr(self, k, sl[k])
+        self._engine = BatchedPlannerLPV(np.eye(9), np.eye(3), np.eye(2), np.eye(2), N, dt, map, 0, mp, sl, nn=0, max_batch=1)
+
+    def sim(self, u):
+        torch = _torch()
+        dev = self._engine.device
+        xp = torch.from_numpy(np.ascontiguousarray(self.xPred, dtype=np.float64)[None]).to(dev)
+        uu = torch.from_numpy(np.ascontiguousarray(u, dtype=np.float64)[None]).to(dev)
+        out, st = self._engine.sim_batch(xp, uu)
+        if int(st.cpu()[0]) != 0:
+            raise DmpcError("curvature()/get_ey() find no segment (misc.py:97,123): status %d" % int(st.cpu()[0]))
+        self.xPred = out[0].cpu().numpy()
+        return self.xPred

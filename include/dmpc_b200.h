@@ -151,6 +151,15 @@ int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A
                            const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
                            void* stream);
 
+/* Batched LPV model roll-out, SURVEY.md 8(f2).  Replaces LPV_Model.sim (LPV_val.py:77-94) with that file's own
+ * linearisation (LPV_val.py:96-195: no low-velocity branch) for B independent models, DEVICE buffers:
+ *   d_xpred [B,N+1,9] = each model's xPred before the call, d_u [B,N,2];
+ *   d_out   [B,N+1,9] = [x_1 .. x_N, ones(9)] (the value sim() returns and stores in xPred); may not alias d_xpred;
+ *   d_status [B] (may be NULL): 0, or DMPC_MAP_LOOKUP_FAILED with NaN rows where the reference raises.
+ * Uses the handle's N, dt, map and vehicle parameters (sys_lim is not used by sim).  Asynchronous. */
+int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, const double* d_u, double* d_out,
+                   int32_t* d_status, void* stream);
+
 /* Engine the handle runs on: DMPC_ENGINE_GENERIC or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
 int dmpc_engine(const dmpc_handle* h);
 

@@ -135,6 +135,22 @@ def osqp_dense(P, q, A, l, u, st=None):
                 rho_updates=int(info[7]))
 
 
+def sim_batch(params, xpred, u):
+    """LPV_val.py:77-94 (LPV_Model.sim) for a batch: xpred (B, N+1, 9), u (B, N, 2) -> (rolled-out and shifted xPred, status)."""
+    N = params.N
+    xpred = np.ascontiguousarray(np.asarray(xpred, dtype=np.float64))
+    B = xpred.shape[0]
+    u = _f64(u, (B, N, 2))
+    out = np.zeros((B, N + 1, 9))
+    status = np.zeros(B, dtype=np.int32)
+    f = lib().oracle_sim_batch
+    f.restype = C.c_int
+    rc = f(C.byref(params), C.c_int(B), _ptr(xpred), _ptr(u), _ptr(out), status.ctypes.data_as(C.c_void_p))
+    if rc:
+        raise RuntimeError("oracle_sim_batch failed: %d" % rc)
+    return out, status
+
+
 def unpack(z, N):
     """LPV_Planner.py:162-180, including the duPred indexing quirk (:175)."""
     z = np.asarray(z)

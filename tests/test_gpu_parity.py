@@ -249,3 +249,44 @@ def test_full_size_batch_properties(built, cfg, track):
     u = out["z"][:, u0:u0 + 2 * N].reshape(-1, N, 2)
     assert u[:, :, 0].max() <= 0.3 + 1e-9 and u[:, :, 0].min() >= -0.3 - 1e-9
     assert u[:, :, 1].max() <= 5.0 + 1e-9 and u[:, :, 1].min() >= -10.0 - 1e-9
+
+
+def test_model_rollout_vs_reference_and_oracle(built, cfg, track):
+    """SURVEY 8(f2), LPV_Model.sim (LPV_val.py:77-94): the CUDA roll-out through the C ABI against (1) the reference's own
+    outputs (golden, 18 cases), (2) the oracle on 1024 synthetic platoon predictions, (3) the drop-in class chained like
+    scripts/eval_LPV_model.py:50-56, (4) a failed map lookup.  FP64; sincos and FMA contraction differ from numpy's
+    libm / matmul order: tolerance 1e-12 relative (achieved ~1e-15)."""
+    import torch
+    from colaborativempc_b200 import scenarios as sc
+    from colaborativempc_b200._abi import make_params
+    from colaborativempc_b200.planner import LPV_Model
+    from oracle import lpv_oracle as lo
+    g = golden("ref_lpv_model_sim_N20.npz")
+    eng = _engine(cfg, track, nn=0, max_batch=1)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    out, st = eng.sim_batch(dev(g["xpred"]), dev(g["u"]))
+    assert np.all(st.cpu().numpy() == 0)
+    assert np.abs(out.cpu().numpy() - g["out"]).max() <= 1e-12 * (1 + np.abs(g["out"]).max())
+    # (2) a batch: states of synthetic platoons, inputs perturbed
+    S, A = 256, 4
+    x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=5)
+    xp = np.ascontiguousarray(xprev.reshape(S * A, N + 1, 9))
+    rng = np.random.default_rng(3)
+    u = np.ascontiguousarray(uprev.reshape(S * A, N, 2) + rng.uniform(-0.05, 0.05, (S * A, N, 2)))
+    P = make_params(*planner_args(cfg, track, N), nn=0)
+    ref, rst = lo.sim_batch(P, xp, u)
+    out, st = eng.sim_batch(dev(xp), dev(u))
+    assert np.array_equal(st.cpu().numpy(), rst) and np.all(rst == 0)
+    assert np.abs(out.cpu().numpy() - ref).max() <= 1e-12 * (1 + np.abs(ref).max())
+    # (3) drop-in class, chained calls
+    m = LPV_Model(N, cfg["dt"], track, model_param=cfg["model_param"], sys_lim=cfg["sys_lim"])
+    m.xPred = g["xpred"][0].copy()
+    for call in range(6):
+        ret = m.sim(g["u"][call])
+        assert np.abs(ret - g["out"][call]).max() <= 1e-12 * (1 + np.abs(g["out"][call]).max())
+    # (4) no segment for a state's s: the reference raises inside curvature()
+    bad = g["xpred"][:2].copy()
+    bad[1, 7, 6] = np.nan
+    out, st = eng.sim_batch(dev(bad), dev(g["u"][:2]))
+    st = st.cpu().numpy()
+    assert st[0] == 0 and st[1] == -20 and np.all(np.isnan(out[1].cpu().numpy())) and not np.isnan(out[0].cpu().numpy()).any()

@@ -167,3 +167,19 @@ def test_map_lookup_edge_cases(P, cfg, track):
     assert o1["status"][0] == 1 and np.array_equal(o1["z"], o2["z"])
     s0, ln, cv, hw = map_table(track)
     assert len(s0) == 10 and ln[0] == 0.0 and ln[-1] == 0.0  # Highway has two zero-length segments
+
+
+def test_model_rollout_matches_reference_lpv_model(P):
+    """oracle restatement of LPV_Model.sim against the REFERENCE's own LPV_Model.sim (fixture made by
+    tests/golden/make_golden_sim.py from the unmodified reference): 3 agents x 6 chained calls.  Only the summation
+    order of the 9-term row products differs (numpy matmul vs a plain loop): 1e-13 relative."""
+    g = golden("ref_lpv_model_sim_N20.npz")
+    out, st = lo.sim_batch(P, g["xpred"], g["u"])
+    assert np.all(st == 0)
+    assert np.abs(out - g["out"]).max() <= 1e-13 * (1 + np.abs(g["out"]).max())
+    assert np.all(out[:, -1, :] == 1.0)                       # np.vstack(..., np.ones((1, 9)))  (LPV_val.py:92)
+    assert np.array_equal(g["xpred"][1], g["out"][0])         # the fixture chains: next call's xPred = previous return
+    bad = g["xpred"][:1].copy()
+    bad[0, 5, 6] = np.nan                                     # curvature() finds no segment: the reference raises
+    out, st = lo.sim_batch(P, bad, g["u"][:1])
+    assert st[0] == -20 and np.all(np.isnan(out))
