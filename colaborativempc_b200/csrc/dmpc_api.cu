@@ -339,6 +339,45 @@ __global__ void shift_pack_kernel(int B, int N, const double* __restrict__ z, do
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// OCD dual update: planner/scripts/NL_EU_N_main.py:122-138 with eval_constraintEU
+// (plan_lib/config/NL/config.py:19-23):  lambdas[s,i,j,k-1] += alpha * (dth - ||p_i,k - p_j,k||), i < j, k = 1..N.
+// One thread per (s, i, j, k) of the upper triangle; consecutive threads walk k, so the lambda row (N doubles) and the
+// two position rows are read and written as contiguous segments.  Roundings as numpy's: no fma contraction.
+__global__ void ocd_lambda_kernel(int S, int A, int N, double alpha, double dth, const double* __restrict__ xy,
+                                  double* __restrict__ lambdas) {
+  const long long npair = (long long)A * (A - 1) / 2;
+  const long long total = (long long)S * npair * N;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(e % N);
+    long long r = e / N;
+    const int pr = (int)(r % npair);
+    const int s = (int)(r / npair);
+    int i = 0, rem = pr;  // pair index -> (i, j), i < j, row-major over the upper triangle
+    while (rem >= A - 1 - i) { rem -= A - 1 - i; ++i; }
+    const int j = i + 1 + rem;
+    const double* pi = xy + (((size_t)s * A + i) * (N + 1) + (k + 1)) * 2;
+    const double* pj = xy + (((size_t)s * A + j) * (N + 1) + (k + 1)) * 2;
+    const double dx = pi[0] - pj[0], dy = pi[1] - pj[1];
+    const double d = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    double* l = lambdas + (((size_t)s * A + i) * A + j) * N + k;
+    *l = __dadd_rn(*l, __dmul_rn(alpha, dth - d));
+  }
+}
+
+extern "C" int dmpc_ocd_lambda_update(dmpc_handle* h, int32_t S, int32_t A, double alpha, double dth, const double* d_xy,
+                                      double* d_lambdas, void* stream) {
+  if (!h || S < 0 || A < 1 || (S > 0 && (!d_xy || !d_lambdas))) return DMPC_ERR_ARG;
+  const long long total = (long long)S * A * (A - 1) / 2 * h->P.N;
+  if (total == 0) return DMPC_OK;
+  const long long want = (total + 255) / 256;
+  const int blocks = (int)(want < 148LL * 8 ? want : 148LL * 8);
+  ocd_lambda_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(S, A, h->P.N, alpha, dth, d_xy, d_lambdas);
+  h->launches++;
+  CUDA_TRY(h, cudaGetLastError());
+  return DMPC_OK;
+}
+
 extern "C" int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, const double* d_u, double* d_out,
                               int32_t* d_status, void* stream) {
   if (!h || B < 0 || (B > 0 && (!d_xpred || !d_u || !d_out))) return DMPC_ERR_ARG;

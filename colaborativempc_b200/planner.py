@@ -174,6 +174,20 @@ class BatchedPlannerLPV(object):
         return out, status
 
 
+    def ocd_lambda_update(self, lambdas, xy, dth, alpha=0.25, stream=None):
+        """In-place dual update of the OCD loop (NL_EU_N_main.py:122-138, Euclidean form) on device tensors:
+        xy [S,A,N+1,2], lambdas [S,A,A,N]; alpha defaults to the reference's get_alpha()."""
+        torch = _torch()
+        S, A = xy.shape[0], xy.shape[1]
+        assert xy.is_cuda and xy.dtype == torch.float64 and xy.is_contiguous() and tuple(xy.shape) == (S, A, self.N + 1, 2)
+        assert lambdas.is_cuda and lambdas.dtype == torch.float64 and lambdas.is_contiguous()
+        assert tuple(lambdas.shape) == (S, A, A, self.N)
+        s = torch.cuda.current_stream(self.device) if stream is None else stream
+        self._check(self.lib.dmpc_ocd_lambda_update(self._h, S, A, float(alpha), float(dth), xy.data_ptr(), lambdas.data_ptr(),
+                                                    C.c_void_p(s.cuda_stream)))
+        return lambdas
+
+
 def unpack_solution(z, N):
     """Views of res.x as PlannerLPV.solve unpacks it (LPV_Planner.py:162-180), incl. the duPred indexing of :175."""
     z = np.asarray(z)

@@ -160,6 +160,15 @@ int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A
 int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, const double* d_u, double* d_out,
                    int32_t* d_status, void* stream);
 
+/* Dual update of the reference's OCD loop, SURVEY.md 8(f4).  Replaces the triple loop of NL_EU_N_main.py:122-138 with
+ * eval_constraintEU (plan_lib/config/NL/config.py:19-23) for S scenarios of A agents, in place, DEVICE buffers:
+ *   d_lambdas[s,i,j,k-1] += alpha * (dth - || d_xy[s,i,k,:] - d_xy[s,j,k,:] ||)   for i < j, k = 1..N;
+ * entries with i >= j are left as they are (the reference adds 0 there).  d_xy [S,A,N+1,2] is the layout
+ * dmpc_shift_pack / the all-gather leave behind, d_lambdas [S,A,A,N].  alpha = get_alpha() = 0.25 in the reference.
+ * Bit-exact with the reference's numpy arithmetic.  Asynchronous. */
+int dmpc_ocd_lambda_update(dmpc_handle* h, int32_t S, int32_t A, double alpha, double dth, const double* d_xy,
+                           double* d_lambdas, void* stream);
+
 /* Engine the handle runs on: DMPC_ENGINE_GENERIC or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
 int dmpc_engine(const dmpc_handle* h);
 

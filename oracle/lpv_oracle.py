@@ -151,6 +151,21 @@ def sim_batch(params, xpred, u):
     return out, status
 
 
+def ocd_lambda_update(lambdas, xy, alpha, dth):
+    """NL_EU_N_main.py:122-138 (Euclidean form): xy (S, A, N+1, 2), lambdas (S, A, A, N) -> updated copy."""
+    xy = np.ascontiguousarray(np.asarray(xy, dtype=np.float64))
+    S, A, N1, _ = xy.shape
+    lam = np.array(lambdas, dtype=np.float64, order="C", copy=True)
+    assert lam.shape == (S, A, A, N1 - 1)
+    f = lib().oracle_ocd_lambda_update
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
+    rc = f(S, A, N1 - 1, float(alpha), float(dth), _ptr(xy), _ptr(lam))
+    if rc:
+        raise RuntimeError("oracle_ocd_lambda_update failed")
+    return lam
+
+
 def unpack(z, N):
     """LPV_Planner.py:162-180, including the duPred indexing quirk (:175)."""
     z = np.asarray(z)

@@ -290,3 +290,30 @@ def test_model_rollout_vs_reference_and_oracle(built, cfg, track):
     out, st = eng.sim_batch(dev(bad), dev(g["u"][:2]))
     st = st.cpu().numpy()
     assert st[0] == 0 and st[1] == -20 and np.all(np.isnan(out[1].cpu().numpy())) and not np.isnan(out[0].cpu().numpy()).any()
+
+
+def test_ocd_dual_update_bit_exact(built, cfg, track):
+    """the CUDA dual update through the C ABI, bit-exact against the reference-generated golden (N=20, the
+    handle's horizon), against the oracle on a larger batch, and a single-agent batch (no pair: nothing changes)."""
+    import torch
+    from oracle import lpv_oracle as lo
+    g = golden("ref_ocd_lambda.npz")
+    eng = _engine(cfg, track, nn=0, max_batch=1)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    lam = dev(g["a_lam0"])
+    xy = dev(g["a_xy"])
+    eng.ocd_lambda_update(lam, xy, float(g["a_dth"]))
+    assert np.array_equal(lam.cpu().numpy(), g["a_lam1"])
+    eng.ocd_lambda_update(lam, xy, float(g["a_dth"]), alpha=float(g["alpha"]))
+    assert np.array_equal(lam.cpu().numpy(), g["a_lam2"])
+    rng = np.random.default_rng(9)
+    S, A = 300, 7
+    xy = rng.normal(size=(S, A, N + 1, 2))
+    lam0 = rng.uniform(-1, 1, size=(S, A, A, N))
+    ref = lo.ocd_lambda_update(lam0, xy, 0.25, 0.3)
+    got = eng.ocd_lambda_update(dev(lam0), dev(xy), 0.3).cpu().numpy()
+    assert np.array_equal(got, ref)
+    one = dev(rng.uniform(size=(4, 1, 1, N)))
+    keep = one.clone()
+    eng.ocd_lambda_update(one, dev(rng.normal(size=(4, 1, N + 1, 2))), 0.3)
+    assert torch.equal(one, keep)

@@ -183,3 +183,18 @@ def test_model_rollout_matches_reference_lpv_model(P):
     bad[0, 5, 6] = np.nan                                     # curvature() finds no segment: the reference raises
     out, st = lo.sim_batch(P, bad, g["u"][:1])
     assert st[0] == -20 and np.all(np.isnan(out))
+
+
+def test_ocd_dual_update_bit_exact_vs_reference():
+    """oracle restatement of the dual update of NL_EU_N_main.py:122-138 against the loop executed with the
+    REFERENCE's eval_constraintEU / get_alpha (tests/golden/make_golden_ocd.py), two chained updates, bit-exact."""
+    g = golden("ref_ocd_lambda.npz")
+    alpha = float(g["alpha"])
+    assert alpha == 0.25
+    for t in "ab":
+        l1 = lo.ocd_lambda_update(g[t + "_lam0"], g[t + "_xy"], alpha, float(g[t + "_dth"]))
+        l2 = lo.ocd_lambda_update(l1, g[t + "_xy"], alpha, float(g[t + "_dth"]))
+        assert np.array_equal(l1, g[t + "_lam1"]) and np.array_equal(l2, g[t + "_lam2"])
+        A = l1.shape[1]
+        low = np.tril_indices(A)                                   # i >= j: untouched (the reference adds zero)
+        assert np.array_equal(l2[:, low[0], low[1], :], g[t + "_lam0"][:, low[0], low[1], :])
