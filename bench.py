@@ -341,6 +341,17 @@ def run_gpu(args):
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
     e2e = {"value": qp_per_step * args.steps / float(t_e2e.item()), "unit": "QP/s", "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * float(t_e2e.item()) / args.steps}
+    if world == 1:
+        # the same call with the page-locked buffers copied through device staging instead of used in place
+        eng.set_options(host_direct=0)
+        e2e_step()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        e2e["staged_value"] = qp_per_step * args.steps / (time.perf_counter() - t0)
+        eng.set_options(host_direct=1)
+        e2e["path"] = ("dmpc_solve_batch_host on page-locked buffers, read/written in place by the kernel over PCIe "
+                       "(host_direct=1); staged_value: same call with H2D/D2H staging copies")
 
     # ---- CPU baseline (rank 0, N=1 only): the reference path restated, on the box's host cores, bounded sample
     cpu = None

@@ -48,7 +48,7 @@ extern "C" void dmpc_default_options(dmpc_options* o) {
   if (!o) return;
   o->polish_delta = 1e-9; o->cert_tol = 1e-9; o->ipm_mu0 = 1e-6;
   o->polish_refine = 4; o->pdas_first = 4; o->pdas_after = 2; o->ipm_max_iter = 60;
-  o->engine = DMPC_ENGINE_AUTO; o->order_hint = 1;
+  o->engine = DMPC_ENGINE_AUTO; o->order_hint = 1; o->host_direct = 1;
 }
 
 static void apply_options(dmpc_handle* h) {
@@ -268,6 +268,22 @@ extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* s
 
 // ---------------------------------------------------------------------------------------------------
 // Host-buffer entry point: H2D of the inputs, solve, D2H of the outputs, all inside the call.
+// Device view of a page-locked host range (cudaHostAlloc / cudaHostRegister memory is mapped into the device's address
+// space under unified addressing); false for pageable memory, device memory, or a range that leaves its allocation.
+static bool pinned_view(const void* p, size_t bytes, void** dev) {
+  *dev = nullptr;
+  if (!p || !bytes) return true;
+  cudaPointerAttributes a, e;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess || cudaPointerGetAttributes(&e, (const char*)p + bytes - 1) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  if (a.type != cudaMemoryTypeHost || e.type != cudaMemoryTypeHost || !a.devicePointer || !e.devicePointer) return false;
+  if ((const char*)e.devicePointer - (const char*)a.devicePointer != (ptrdiff_t)(bytes - 1)) return false;
+  *dev = a.devicePointer;
+  return true;
+}
+
 extern "C" int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io) {
   if (!h || !io) return DMPC_ERR_ARG;
   if (io->B == 0) return DMPC_OK;
@@ -275,6 +291,35 @@ extern "C" int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io) {
   const int N = h->P.N, nn = h->P.nn, B = io->B, rows = io->xprev_rows;
   if (rows < N) return fail(h, DMPC_ERR_ARG, "Last_xPredicted needs at least N rows%s");
   const size_t n = 16 * (size_t)N + 12, mi = (8 + (size_t)nn) * N, me = 14 * (size_t)N + 12;
+  if (h->opt.host_direct && rows <= N + 1) {
+    // Page-locked host buffers: the solve kernel reads its ~3 KB of inputs per QP and writes its results straight
+    // through the PCIe mapping, so the transfers of one QP overlap the arithmetic of the others and no copy sits in
+    // front of or behind the launch.  Any pageable / unmapped buffer sends the whole call down the staging path below.
+    CUDA_TRY(h, cudaSetDevice(h->device));
+    dmpc_batch_io dio = *io;
+    void* v[15];
+    const size_t Bz = (size_t)B;
+    bool ok = pinned_view(io->x0, Bz * 9 * 8, &v[0]) && pinned_view(io->xprev, Bz * rows * 9 * 8, &v[1]) &&
+              pinned_view(io->uprev, Bz * N * 2 * 8, &v[2]) && pinned_view(io->uold, Bz * 2 * 8, &v[3]) &&
+              pinned_view(io->nbr_xy, Bz * (N + 1) * nn * 2 * 8, &v[4]) && pinned_view(io->pose, Bz * (N + 1) * 2 * 8, &v[5]) &&
+              pinned_view(io->nbr_count, Bz * 4, &v[6]) && pinned_view(io->z, Bz * n * 8, &v[7]) &&
+              pinned_view(io->planes, Bz * N * 3 * nn * 8, &v[8]) && pinned_view(io->y_ineq, Bz * mi * 8, &v[9]) &&
+              pinned_view(io->y_eq, Bz * me * 8, &v[10]) && pinned_view(io->obj, Bz * 8, &v[11]) &&
+              pinned_view(io->status, Bz * 4, &v[12]) && pinned_view(io->iters, Bz * 4, &v[13]) &&
+              pinned_view(io->pivots, Bz * 4, &v[14]);
+    if (ok) {
+      if (!h->host_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->host_stream, cudaStreamNonBlocking));
+      dio.x0 = (const double*)v[0]; dio.xprev = (const double*)v[1]; dio.uprev = (const double*)v[2];
+      dio.uold = (const double*)v[3]; dio.nbr_xy = (const double*)v[4]; dio.pose = (const double*)v[5];
+      dio.nbr_count = (const int32_t*)v[6]; dio.z = (double*)v[7]; dio.planes = (double*)v[8]; dio.y_ineq = (double*)v[9];
+      dio.y_eq = (double*)v[10]; dio.obj = (double*)v[11]; dio.status = (int32_t*)v[12]; dio.iters = (int32_t*)v[13];
+      dio.pivots = (int32_t*)v[14];
+      const int rc = dmpc_solve_batch(h, &dio, (void*)h->host_stream);
+      if (rc) return rc;
+      CUDA_TRY(h, cudaStreamSynchronize(h->host_stream));
+      return DMPC_OK;
+    }
+  }
   const size_t Bm = (size_t)h->max_batch;
   // fixed staging layout sized for max_batch (offsets in bytes, 256-aligned)
   size_t off = 0;
@@ -382,12 +427,13 @@ extern "C" int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, 
                               int32_t* d_status, void* stream) {
   if (!h || B < 0 || (B > 0 && (!d_xpred || !d_u || !d_out))) return DMPC_ERR_ARG;
   if (B == 0) return DMPC_OK;
-  const size_t smem = (size_t)SIM_WARPS * h->P.N * 31 * sizeof(double);
+  const size_t smem = (size_t)SIM_WARPS * SIM_GROUP * h->P.N * 30 * sizeof(double);
   if (smem > 48 * 1024 && !h->sim_attr) {
     CUDA_TRY(h, cudaFuncSetAttribute(lpv_sim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     h->sim_attr = 1;
   }
-  lpv_sim_kernel<<<(B + SIM_WARPS - 1) / SIM_WARPS, 32 * SIM_WARPS, smem, (cudaStream_t)stream>>>(h->P, B, d_xpred, d_u, d_out, d_status);
+  const int per_cta = SIM_WARPS * SIM_GROUP;
+  lpv_sim_kernel<<<(B + per_cta - 1) / per_cta, 32 * SIM_WARPS, smem, (cudaStream_t)stream>>>(h->P, B, d_xpred, d_u, d_out, d_status);
   h->launches++;
   CUDA_TRY(h, cudaGetLastError());
   return DMPC_OK;

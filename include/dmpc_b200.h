@@ -65,6 +65,10 @@ typedef struct dmpc_options {
                              batch size spent on each QP index (most expensive first, the interior-point ones alone on
                              an SM; consecutive MPC steps are alike).  Scheduling only: results are independent of it.
                              Calls on one handle must then be stream-ordered with each other.  0 = off               */
+  int32_t host_direct;    /* dmpc_solve_batch_host: 1 = when every buffer of the call is page-locked host memory
+                             (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory) the kernel reads and writes it
+                             in place over PCIe instead of staging copies; pageable buffers always take the staged
+                             path.  Results are identical.  0 = always stage                                         */
 } dmpc_options;
 
 /* Per-QP status values mirror OSQP's status_val so `feasible` is derived as LPV_Planner.py:246-248. */

@@ -29,7 +29,7 @@ def test_struct_layout_matches_header(built):
     from oracle import lpv_oracle as lo
     assert lo.lib().oracle_sizeof_params() == C.sizeof(_abi.DmpcParams)
     # dmpc_options: 3 doubles + 6 int32; dmpc_batch_io: 2 int32 + 15 pointers
-    assert C.sizeof(_abi.DmpcOptions) == 3 * 8 + 6 * 4
+    assert C.sizeof(_abi.DmpcOptions) == 3 * 8 + 8 * 4  # 7 ints, padded to the doubles' alignment
     assert C.sizeof(_abi.DmpcBatchIO) == 8 + 15 * 8
 
 

@@ -147,6 +147,31 @@ def test_device_and_host_entry_points_agree(built, cfg, track):
     assert eng.launches == (5 if eng.fast else 2)
 
 
+def test_page_locked_host_buffers_are_used_in_place(built, cfg, track):
+    """dmpc_options.host_direct: with page-locked buffers the kernel reads/writes host memory in place over PCIe (no
+    staging copies); the results are bit-identical with the staged path, also when only some buffers are page-locked
+    (the whole call is then staged) and for a view at an offset inside a page-locked allocation."""
+    import torch
+    fx = golden("platoon_N20.npz")
+    ins = {k: fx["it3_%s" % k] for k in INPUT_KEYS}
+    staged = _engine(cfg, track, options={"host_direct": 0}).solve_batch_host(**ins)
+    eng = _engine(cfg, track)
+    B = ins["x0"].shape[0]
+
+    def pinned(a, pad=0):  # a copy of `a` living `pad` elements into a page-locked allocation
+        t = torch.empty((a.size + pad,), dtype=torch.from_numpy(a).dtype).pin_memory()
+        v = t.numpy()[pad:].reshape(a.shape)
+        v[...] = a
+        return v
+    for pad, partial in ((0, False), (3, False), (0, True)):
+        p_in = {k: (None if v is None else (np.ascontiguousarray(v) if partial and k == "xprev" else pinned(np.ascontiguousarray(v), pad)))
+                for k, v in ins.items()}
+        p_out = {k: pinned(np.full_like(v, -7), pad) for k, v in staged.items()}
+        got = eng.solve_batch_host(out=p_out, **p_in)
+        for k in staged:
+            assert np.array_equal(got[k], staged[k]), (k, pad, partial)
+
+
 def test_cost_ordered_launch_changes_nothing(built, cfg, track):
     """order_hint only permutes which CTA solves which QP (most expensive of the previous call first): outputs are
     bit-identical with the hint off, on the first call (identity order) and on later calls (sorted order), also when
@@ -249,6 +274,45 @@ def test_full_size_batch_properties(built, cfg, track):
     u = out["z"][:, u0:u0 + 2 * N].reshape(-1, N, 2)
     assert u[:, :, 0].max() <= 0.3 + 1e-9 and u[:, :, 0].min() >= -0.3 - 1e-9
     assert u[:, :, 1].max() <= 5.0 + 1e-9 and u[:, :, 1].min() >= -10.0 - 1e-9
+
+
+def test_device_loop_and_run_log(built, cfg, track, tmp_path):
+    """`ShardedDMPC.iterate` (gather -> solve -> shift/pack -> exchange, all on the device) reproduces the
+    host-driven loop of LPV_HP_N_main.py:96-117 bit for bit, and `run_closed_loop` logs what the reference's agents log
+    (base_class.py:47-62) and stops on the reference's end-of-track rule (misc.py:28-48)."""
+    import torch
+    from colaborativempc_b200 import scenarios as sc
+    from colaborativempc_b200.dmpc import ShardedDMPC
+    from colaborativempc_b200.runlog import RunLog, run_closed_loop
+    S, A, iters = 4, 3, 5
+    x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=300)
+    idx, cnt = sc.topology(A, "full")
+    rec, host_eng = [], _engine(cfg, track, max_batch=S * A)
+    sc.run_dmpc(lambda **kw: host_eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, iters, N, record=rec)
+    dm = ShardedDMPC(_engine(cfg, track, max_batch=S * A), S, A, idx, cnt, x0, xprev, uprev)
+    for it in range(iters):
+        out = dm.iterate()
+        torch.cuda.synchronize()
+        assert np.array_equal(out["z"].cpu().numpy(), rec[it][1]["z"]), it
+        assert np.array_equal(out["status"].cpu().numpy(), rec[it][1]["status"])
+    # the logged run: scenario 1, a track "ending" 0.6 m ahead of the leading agent so that the end rule fires
+    dm = ShardedDMPC(_engine(cfg, track, max_batch=S * A), S, A, idx, cnt, x0, xprev, uprev)
+    logs = [RunLog(a, str(tmp_path) + "/") for a in range(A)]
+    L = float(x0[1, :, 6].max()) + 0.6
+    n_it, ended, error = run_closed_loop(dm, L, 200, logs=logs, log_scenario=1)
+    assert ended and not error and 0 < n_it < 200
+    zs = [r[1]["z"].reshape(S, A, -1)[1] for r in rec]
+    for a, lg in enumerate(logs):
+        assert len(lg.states) == len(lg.u) == len(lg.look_ahead) == len(lg.time_op) == n_it
+        for t in range(min(n_it, iters)):
+            xs = zs[t][a][:12 * (N + 1)].reshape(N + 1, 12)
+            assert np.array_equal(lg.states[t], xs[0, :9]) and lg.look_ahead[t] == xs[-1, 6] - xs[0, 6]
+            assert np.array_equal(lg.u[t], zs[t][a][12 * (N + 1):12 * (N + 1) + 2])
+            assert np.array_equal(lg.planes[t], rec[t][1]["planes"].reshape(S, A, N, 3, -1)[1, a, 0])
+        path = lg.save_to_csv()
+        assert np.loadtxt(path + "/states.dat").reshape(n_it, 9).shape == (n_it, 9)
+    s_last = max(lg.states[-1][6] for lg in logs)
+    assert s_last < L + 0.5  # stopped at the first iteration whose row 0 passed L - 0.15
 
 
 def test_model_rollout_vs_reference_and_oracle(built, cfg, track):
