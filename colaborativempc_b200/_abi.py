@@ -106,7 +106,7 @@ def default_lib_path():
 EXPORTS = ["dmpc_default_options", "dmpc_version", "dmpc_create", "dmpc_destroy", "dmpc_last_error",
            "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
            "dmpc_gather_neighbours", "dmpc_launch_count", "dmpc_engine", "dmpc_sim_batch",
-           "dmpc_ocd_lambda_update"]
+           "dmpc_ocd_lambda_update", "dmpc_ocd_lambda_update_hp"]
 
 _lib = None
 
@@ -148,6 +148,9 @@ def load_library(path=None):
     lib.dmpc_ocd_lambda_update.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_void_p, C.c_void_p,
                                            C.c_void_p]
     lib.dmpc_ocd_lambda_update.restype = C.c_int
+    lib.dmpc_ocd_lambda_update_hp.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_void_p]
+    lib.dmpc_ocd_lambda_update_hp.restype = C.c_int
     lib.dmpc_launch_count.argtypes = [C.c_void_p]
     lib.dmpc_launch_count.restype = C.c_int64
     if path == default_lib_path():

@@ -423,6 +423,48 @@ extern "C" int dmpc_ocd_lambda_update(dmpc_handle* h, int32_t S, int32_t A, doub
   return DMPC_OK;
 }
 
+// Hyperplane form of the same update: planner/scripts/NL_HP_N_main.py:128-137 with eval_constraintHp
+// (plan_lib/config/NL/config.py:25-29):  cost = -a_x x_j,k - a_y y_j,k - b + dth/2 with (a_x, a_y, b) =
+// planes_raw[i][k-1, :, j], i < j, k = 1..N.  planes [S, A(i), N, 3, A(j)] is the stack of the planes every agent's
+// solve returned.  Same thread mapping as above; the plane triple is a strided read (stride A doubles), the position
+// and lambda rows are contiguous.  Operation order and roundings as numpy evaluates the expression, left to right.
+__global__ void ocd_lambda_hp_kernel(int S, int A, int N, double alpha, double dth, const double* __restrict__ xy,
+                                     const double* __restrict__ planes, double* __restrict__ lambdas) {
+  const long long npair = (long long)A * (A - 1) / 2;
+  const long long total = (long long)S * npair * N;
+  const double half = dth / 2;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(e % N);
+    long long r = e / N;
+    const int pr = (int)(r % npair);
+    const int s = (int)(r / npair);
+    int i = 0, rem = pr;
+    while (rem >= A - 1 - i) { rem -= A - 1 - i; ++i; }
+    const int j = i + 1 + rem;
+    const double* pj = xy + (((size_t)s * A + j) * (N + 1) + (k + 1)) * 2;
+    const double* pl = planes + ((((size_t)s * A + i) * N + k) * 3) * A + j;
+    double c = __dmul_rn(-pl[0], pj[0]);
+    c = __dsub_rn(c, __dmul_rn(pl[A], pj[1]));
+    c = __dsub_rn(c, pl[2 * (size_t)A]);
+    c = __dadd_rn(c, half);
+    double* l = lambdas + (((size_t)s * A + i) * A + j) * N + k;
+    *l = __dadd_rn(*l, __dmul_rn(alpha, c));
+  }
+}
+
+extern "C" int dmpc_ocd_lambda_update_hp(dmpc_handle* h, int32_t S, int32_t A, double alpha, double dth, const double* d_xy,
+                                         const double* d_planes, double* d_lambdas, void* stream) {
+  if (!h || S < 0 || A < 1 || (S > 0 && (!d_xy || !d_planes || !d_lambdas))) return DMPC_ERR_ARG;
+  const long long total = (long long)S * A * (A - 1) / 2 * h->P.N;
+  if (total == 0) return DMPC_OK;
+  const long long want = (total + 255) / 256;
+  const int blocks = (int)(want < 148LL * 8 ? want : 148LL * 8);
+  ocd_lambda_hp_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(S, A, h->P.N, alpha, dth, d_xy, d_planes, d_lambdas);
+  h->launches++;
+  CUDA_TRY(h, cudaGetLastError());
+  return DMPC_OK;
+}
+
 extern "C" int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, const double* d_u, double* d_out,
                               int32_t* d_status, void* stream) {
   if (!h || B < 0 || (B > 0 && (!d_xpred || !d_u || !d_out))) return DMPC_ERR_ARG;

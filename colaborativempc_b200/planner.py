@@ -187,6 +187,18 @@ class BatchedPlannerLPV(object):
                                                     C.c_void_p(s.cuda_stream)))
         return lambdas
 
+    def ocd_lambda_update_hp(self, lambdas, xy, planes, dth, alpha=0.25, stream=None):
+        """In-place dual update of the OCD loop, hyperplane form (NL_HP_N_main.py:128-137 with eval_constraintHp) on
+        device tensors: xy [S,A,N+1,2], planes [S,A,N,3,A] (agent i's planes_raw stacked over i), lambdas [S,A,A,N]."""
+        torch = _torch()
+        S, A = xy.shape[0], xy.shape[1]
+        for t, shp in ((xy, (S, A, self.N + 1, 2)), (planes, (S, A, self.N, 3, A)), (lambdas, (S, A, A, self.N))):
+            assert t.is_cuda and t.dtype == torch.float64 and t.is_contiguous() and tuple(t.shape) == shp
+        s = torch.cuda.current_stream(self.device) if stream is None else stream
+        self._check(self.lib.dmpc_ocd_lambda_update_hp(self._h, S, A, float(alpha), float(dth), xy.data_ptr(),
+                                                       planes.data_ptr(), lambdas.data_ptr(), C.c_void_p(s.cuda_stream)))
+        return lambdas
+
 
 def unpack_solution(z, N):
     """Views of res.x as PlannerLPV.solve unpacks it (LPV_Planner.py:162-180), incl. the duPred indexing of :175."""

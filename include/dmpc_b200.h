@@ -173,6 +173,15 @@ int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, const doubl
 int dmpc_ocd_lambda_update(dmpc_handle* h, int32_t S, int32_t A, double alpha, double dth, const double* d_xy,
                            double* d_lambdas, void* stream);
 
+/* Hyperplane form of the OCD dual update.  Replaces the triple loop of NL_HP_N_main.py:128-137 with eval_constraintHp
+ * (plan_lib/config/NL/config.py:25-29), in place, DEVICE buffers:
+ *   d_lambdas[s,i,j,k-1] += alpha * (-a_x * x - a_y * y - b + dth/2),  (a_x,a_y,b) = d_planes[s,i,k-1,:,j],
+ *   (x,y) = d_xy[s,j,k,:],  for i < j, k = 1..N;  entries with i >= j are left as they are.
+ * d_planes [S,A,N,3,A] stacks the planes each agent's solve returned (planes_raw[i][k-1,:,j], j = absolute agent
+ * index).  Bit-exact with the reference's numpy arithmetic.  Asynchronous. */
+int dmpc_ocd_lambda_update_hp(dmpc_handle* h, int32_t S, int32_t A, double alpha, double dth, const double* d_xy,
+                              const double* d_planes, double* d_lambdas, void* stream);
+
 /* Engine the handle runs on: DMPC_ENGINE_GENERIC or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
 int dmpc_engine(const dmpc_handle* h);
 

@@ -166,6 +166,22 @@ def ocd_lambda_update(lambdas, xy, alpha, dth):
     return lam
 
 
+def ocd_lambda_update_hp(lambdas, xy, planes, alpha, dth):
+    """NL_HP_N_main.py:128-137 (hyperplane form): xy (S, A, N+1, 2), planes (S, A, N, 3, A), lambdas (S, A, A, N)."""
+    xy = np.ascontiguousarray(np.asarray(xy, dtype=np.float64))
+    planes = np.ascontiguousarray(np.asarray(planes, dtype=np.float64))
+    S, A, N1, _ = xy.shape
+    lam = np.array(lambdas, dtype=np.float64, order="C", copy=True)
+    assert lam.shape == (S, A, A, N1 - 1) and planes.shape == (S, A, N1 - 1, 3, A)
+    f = lib().oracle_ocd_lambda_update_hp
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
+    rc = f(S, A, N1 - 1, float(alpha), float(dth), _ptr(xy), _ptr(planes), _ptr(lam))
+    if rc:
+        raise RuntimeError("oracle_ocd_lambda_update_hp failed")
+    return lam
+
+
 def unpack(z, N):
     """LPV_Planner.py:162-180, including the duPred indexing quirk (:175)."""
     z = np.asarray(z)

@@ -381,3 +381,15 @@ def test_ocd_dual_update_bit_exact(built, cfg, track):
     keep = one.clone()
     eng.ocd_lambda_update(one, dev(rng.normal(size=(4, 1, N + 1, 2))), 0.3)
     assert torch.equal(one, keep)
+    # hyperplane form (NL_HP_N_main.py:128-137): reference-generated golden, then a larger batch against the oracle
+    lam = dev(g["hp_a_lam0"])
+    xy, pl = dev(g["hp_a_xy"]), dev(g["hp_a_planes"])
+    eng.ocd_lambda_update_hp(lam, xy, pl, float(g["hp_a_dth"]))
+    assert np.array_equal(lam.cpu().numpy(), g["hp_a_lam1"])
+    eng.ocd_lambda_update_hp(lam, xy, pl, float(g["hp_a_dth"]), alpha=float(g["alpha"]))
+    assert np.array_equal(lam.cpu().numpy(), g["hp_a_lam2"])
+    xy = rng.normal(size=(S, A, N + 1, 2))
+    pl = rng.normal(size=(S, A, N, 3, A))
+    ref = lo.ocd_lambda_update_hp(lam0, xy, pl, 0.25, 0.3)
+    got = eng.ocd_lambda_update_hp(dev(lam0), dev(xy), dev(pl), 0.3).cpu().numpy()
+    assert np.array_equal(got, ref)

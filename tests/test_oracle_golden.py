@@ -198,3 +198,15 @@ def test_ocd_dual_update_bit_exact_vs_reference():
         A = l1.shape[1]
         low = np.tril_indices(A)                                   # i >= j: untouched (the reference adds zero)
         assert np.array_equal(l2[:, low[0], low[1], :], g[t + "_lam0"][:, low[0], low[1], :])
+
+
+def test_ocd_dual_update_hyperplane_form_bit_exact_vs_reference():
+    """Hyperplane form (NL_HP_N_main.py:128-137, eval_constraintHp): same fixture script, same bar."""
+    g = golden("ref_ocd_lambda.npz")
+    alpha = float(g["alpha"])
+    for t in ("hp_a", "hp_b"):
+        l1 = lo.ocd_lambda_update_hp(g[t + "_lam0"], g[t + "_xy"], g[t + "_planes"], alpha, float(g[t + "_dth"]))
+        l2 = lo.ocd_lambda_update_hp(l1, g[t + "_xy"], g[t + "_planes"], alpha, float(g[t + "_dth"]))
+        assert np.array_equal(l1, g[t + "_lam1"]) and np.array_equal(l2, g[t + "_lam2"])
+        low = np.tril_indices(l1.shape[1])
+        assert np.array_equal(l2[:, low[0], low[1], :], g[t + "_lam0"][:, low[0], low[1], :])
