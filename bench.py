@@ -192,7 +192,8 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    if world == 1:
+    single = world == 1 and args.workload == "batch"  # --workload dmpc: the N>1 step (sharded closed loop) on one GPU
+    if single:
         A = 3
         S = (BATCH + A - 1) // A
         eng = BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=NN, max_batch=S * A)
@@ -249,7 +250,7 @@ def run_gpu(args):
 
     # ---- the same steps with the cost-ordered launch off (blockIdx = QP index): what a cold, never-seen batch costs
     unordered = None
-    if world == 1 and eng.fast:
+    if single and eng.fast:
         eng.set_options(order_hint=0)
         step()
         torch.cuda.synchronize()
@@ -269,7 +270,7 @@ def run_gpu(args):
         torch.cuda.synchronize()
 
     # ---- dominant kernel (lpv_qp_solve_kernel) timed alone on its launch stream, for the roofline object
-    if world == 1:
+    if single:
         kern_ms = total_ms / args.steps
         kern_qps = BATCH
     else:
@@ -306,7 +307,7 @@ def run_gpu(args):
                         "so the HBM fraction is small by construction"}
 
     # ---- end to end through the host-buffer C-ABI call: pinned host inputs -> H2D -> solve -> D2H, every step
-    if world == 1:
+    if single:
         pin = lambda a: torch.from_numpy(a).pin_memory().numpy()
         h_in = {k: pin(v) for k, v in ins.items()}
         h_out = dict(z=pin(np.empty((BATCH, eng.n))), planes=pin(np.empty((BATCH, HORIZON, 3, NN))), obj=pin(np.empty(BATCH)),
@@ -341,7 +342,7 @@ def run_gpu(args):
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
     e2e = {"value": qp_per_step * args.steps / float(t_e2e.item()), "unit": "QP/s", "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * float(t_e2e.item()) / args.steps}
-    if world == 1:
+    if single:
         # the same call with the page-locked buffers copied through device staging instead of used in place
         eng.set_options(host_direct=0)
         e2e_step()
@@ -355,7 +356,7 @@ def run_gpu(args):
 
     # ---- CPU baseline (rank 0, N=1 only): the reference path restated, on the box's host cores, bounded sample
     cpu = None
-    if world == 1 and not args.no_cpu_baseline:
+    if single and not args.no_cpu_baseline:
         cores = len(os.sched_getaffinity(0))
         sample = max(48, min(BATCH, 256 * cores))
         rate, secs, o = cpu_reference_rate(ins, cfg, track, cores, sample)
@@ -390,6 +391,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="batch", choices=["batch", "dmpc"],
+                    help="N=1 only: 'dmpc' runs the multi-GPU step (16-agent platoons, closed loop) on one GPU")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
