@@ -100,6 +100,36 @@ def test_reference_startup_case(built, cfg, track):
     _compare(out, o["z"], o["y"], o["obj"], o["planes"], eng.m_in)
 
 
+def test_recorded_reference_run_horizon_125(built, cfg, track):
+    """The reference's recorded experiment (LPV3r_agent_laptop, N=125): its first DMPC iteration from the reference's
+    cold start through the CUDA path (generic engine, global-memory workspace).  Parity with the oracle's certified
+    optimum at 1e-6; against the recorded uPred - an un-polished OSQP iterate at eps 1e-3, see
+    test_restated_osqp_reproduces_the_reference_recorded_run - the optimum sits within 0.1 (9.1e-2 / 5.9e-2 / 4.2e-2,
+    SURVEY 8c), and the recorded point's objective is not better than ours once its constraint violation is paid for."""
+    from colaborativempc_b200 import scenarios as sc
+    rec = golden("recorded_N125_it0.npz")
+    Nh = 125
+    eng = _engine(cfg, track, N=Nh, nn=2, max_batch=3)
+    agents, xs, us = sc.initialise_agents(sc.X0_DATABASE[0:3], Nh, cfg["dt"], track)
+    idx, cnt = sc.topology(3, "full", nn=2)
+    log = []
+    sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), np.stack([x[0] for x in xs])[None], np.stack(xs)[None],
+                np.stack(us)[None], idx, cnt, 1, Nh, record=log)
+    ins, out = log[0]
+    assert np.all(np.isin(out["status"], (1, 2)))
+    o = _oracle(cfg, track, ins, N=Nh, nn=2, nthreads=3)
+    assert np.all(o["status"] == 1)
+    u0 = 12 * (Nh + 1)
+    for i in range(3):
+        tol = TOL if out["status"][i] == 1 else 1e-5
+        assert rel_err(out["z"][i:i + 1], o["z"][i:i + 1]).max() < tol
+        assert abs(out["obj"][i] - o["obj"][i]) < TOL * abs(o["obj"][i])
+        u = out["z"][i, u0:u0 + 2 * Nh].reshape(Nh, 2)
+        assert np.abs(u - rec["u_it0_agent%d" % i]).max() < 0.1
+        if out["status"][i] == 1:
+            _kkt_certificate(cfg, track, ins, out, i, Nh, 2)
+
+
 @pytest.mark.parametrize("Nh,nn,topo,S,A", [(10, 2, "full", 8, 3), (20, 2, "chain", 4, 6), (20, 5, "full", 4, 6),
                                             (50, 2, "full", 4, 3), (20, 0, "full", 8, 1)])
 def test_closed_loop_vs_oracle(built, cfg, track, Nh, nn, topo, S, A):
