@@ -133,7 +133,10 @@ int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt);
  * `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  Asynchronous. */
 int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* stream);
 
-/* Same call with HOST buffers: pinned staging + H2D, solve, D2H inside (the end-to-end path). Synchronous. */
+/* Same call with HOST buffers (the end-to-end path).  Synchronous.  Pageable buffers: copied to page-locked staging,
+ * H2D, solve, D2H.  If every buffer of the call is page-locked (cudaHostAlloc / cudaHostRegister) and
+ * dmpc_options.host_direct = 1 (default) the kernel reads and writes them in place over PCIe - no staging copies,
+ * same results bit for bit. */
 int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io);
 
 /* Caller-side bookkeeping of one DMPC iteration (LPV_HP_N_main.py:106,113-117), on device:
