@@ -212,10 +212,15 @@ def run_gpu(args):
         idx, cnt = sc.topology(A, "chain", nn=NN)
         dm = ShardedDMPC(eng, S, A, idx, cnt, x0, xprev, uprev, rank=rank, world=world)
         step = dm.iterate
+        # cold-start platoons first close their gaps (more saturated QPs per iteration than in cruise): let the closed loop
+        # settle before the warm-up, as config[1]'s batch is taken "at steady state"; --settle 0 times the transient
+        for _ in range(args.settle):
+            step()
         qp_per_step = dm.B * world
         d_out = dm.out
         workload = ("DMPC iteration: %d scenarios x 16-agent chain platoon (nn<=2), N=20, agents sharded %d per GPU "
-                    "(4096 QPs per GPU), one NCCL all-gather of (x,y) predictions per iteration, closed loop" % (S, A // world))
+                    "(4096 QPs per GPU), one NCCL all-gather of (x,y) predictions per iteration, closed loop, timed after %d settling "
+                    "iterations + warm-up" % (S, A // world, args.settle))
         par = "agents sharded over %d GPUs, all-gather per iteration" % world
 
     for _ in range(max(args.warmup, 3)):
@@ -395,6 +400,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--settle", type=int, default=30, help="DMPC workload: closed-loop iterations before warm-up")
     ap.add_argument("--workload", default="batch", choices=["batch", "dmpc"],
                     help="N=1 only: 'dmpc' runs the multi-GPU step (16-agent platoons, closed loop) on one GPU")
     args = ap.parse_args()
