@@ -402,8 +402,8 @@ __device__ __forceinline__ int solve_qp2(const Ctx2& c) {
 #pragma unroll 1
   while (mu_tol > 1e-13) {
     const int rc = ipm2(mu_tol, mu_ok > 0.0);
-    if (rc == 1) {  // divergence of the FIRST phase = infeasible hard rows; later (tighter) phases can only lose accuracy
-      if (mu_ok == 0.0) return DMPC_PRIMAL_INFEASIBLE;
+    if (rc == 1 || rc == 3) {  // divergence of the FIRST phase = infeasible hard rows; later (tighter) phases can only lose accuracy
+      if (mu_ok == 0.0) return rc == 3 ? DMPC_UNSOLVED : DMPC_PRIMAL_INFEASIBLE;  // NaN is a numerical failure, not a certificate
       break;
     }
     if (rc == 0) { mu_ok = mu_tol; ipm_keep2(c, 1); }

@@ -187,7 +187,7 @@ __device__ __forceinline__ void ipm_keep2(const Ctx2& c, int save) {
 
 // Mehrotra predictor-corrector on the condensed QP down to complementarity mu_tol.  warm: continue from the iterate
 // kept in c.sv (the previous, looser phase) instead of building a starting point.
-// Returns 0 converged, 1 diverged (only a QP with infeasible hard rows does that), 2 iteration cap.
+// Returns 0 converged, 1 diverged (only a QP with infeasible hard rows does that), 2 iteration cap, 3 NaN (breakdown).
 __device__ __noinline__ int ipm2(double mu_tol, int warm) {
   CTX2_LOCAL(c);
   const double* Qs = c.hd->Qs;
@@ -280,7 +280,8 @@ __device__ __noinline__ int ipm2(double mu_tol, int warm) {
     const double obj = fabs(block_sum(v_obj, c.red));
     const double lmax = block_max(v_lm, c.red);  // the dual residual carries the rounding of A' lam: scale with it
     if (threadIdx.x == 0) ++((Hdr2*)smem_fast)->n_ipm;
-    if (!(mu == mu) || !(mu < 1e40) || !(rd < 1e40)) return 1;
+    if (!isfinite(mu) || !isfinite(rd)) return 3;  // NaN/inf: the factorisation broke down (ill-conditioned condensed H), not a verdict
+    if (!(mu < 1e40) || !(rd < 1e40)) return 1;
     if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * (gmax + lmax)) return 0;
     // ---- factorise for D = lam / t
 #pragma unroll 1

@@ -131,7 +131,7 @@ __device__ __forceinline__ double step_to_boundary(const Ctx& c, const double* x
 }
 
 // Mehrotra predictor-corrector on the condensed QP down to complementarity mu_tol.
-// Returns 0 converged, 1 diverged (only a QP with infeasible hard rows does that), 2 iteration cap.
+// Returns 0 converged, 1 diverged (only a QP with infeasible hard rows does that), 2 iteration cap, 3 NaN (breakdown).
 __device__ __forceinline__ int ipm(const Ctx& c, const DevParams& P, double mu_tol, int* iters) {
   const int m = c.N * (4 + c.cnt) + 4 * c.N;
   // ---- starting point: least squares with unit row weights, then shift into the cone
@@ -202,7 +202,8 @@ __device__ __forceinline__ int ipm(const Ctx& c, const DevParams& P, double mu_t
     const double obj = fabs(block_sum(v_obj, c.red));
     const double lmax = block_max(v_lm, c.red);  // the dual residual carries the rounding of A' lam: scale with it
     *iters = it;
-    if (!(mu == mu) || !(mu < 1e40) || !(rd < 1e40)) return 1;
+    if (!isfinite(mu) || !isfinite(rd)) return 3;  // NaN/inf: the factorisation broke down (ill-conditioned condensed H), not a verdict
+    if (!(mu < 1e40) || !(rd < 1e40)) return 1;
     if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * (gmax + lmax)) return 0;
     // ---- factorise for D = lam / t
     for (int j = threadIdx.x; j < c.RT; j += QP_THREADS) c.D[j] = row_valid(c, j) ? c.lam[j] / c.tt[j] : 0.0;
@@ -270,8 +271,8 @@ __device__ __forceinline__ int solve_qp(const Ctx& c, const DevParams& P, int* n
     int its = 0;
     const int rc = ipm(c, P, mu_tol, &its);
     *n_ipm += its;
-    if (rc == 1) {  // divergence of the FIRST phase = infeasible hard rows; later (tighter) phases can only lose accuracy
-      if (mu_ok == 0.0) return DMPC_PRIMAL_INFEASIBLE;
+    if (rc == 1 || rc == 3) {  // divergence of the FIRST phase = infeasible hard rows; later (tighter) phases can only lose accuracy
+      if (mu_ok == 0.0) return rc == 3 ? DMPC_UNSOLVED : DMPC_PRIMAL_INFEASIBLE;  // NaN is a numerical failure, not a certificate
       break;
     }
     if (rc == 0) mu_ok = mu_tol;

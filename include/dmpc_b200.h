@@ -80,7 +80,7 @@ enum dmpc_status {
   DMPC_DUAL_INFEASIBLE = -4,
   DMPC_MAP_LOOKUP_FAILED = -20, /* curvature()/get_ey() find no segment (misc.py:97: int() of an empty index raises) */
   DMPC_DEGENERATE_PLANE = -21,  /* ego and neighbour coincide: compute_plane.py:52 divides by zero        */
-  DMPC_UNSOLVED = -10
+  DMPC_UNSOLVED = -10           /* numerical breakdown (NaN in the condensed factorisation): no verdict on the QP         */
 };
 
 enum dmpc_engine { DMPC_ENGINE_AUTO = 0, DMPC_ENGINE_GENERIC = 1, DMPC_ENGINE_FAST = 2 };

@@ -39,6 +39,15 @@ def main(iters=80):
                 print("flush %d it %3d  %.3f ms  ipm/QP %.3f  rounds/QP %.2f  unsolved %d" % (
                     do_flush, it, e0.elapsed_time(e1), out["iters"].double().mean().item(),
                     out["pivots"].double().mean().item(), int((st != 1).sum())), flush=True)
+        st = out["status"].cpu().numpy()
+        bad = np.flatnonzero(st != 1)
+        z = out["z"].cpu().numpy()
+        print("final status histogram", dict(zip(*np.unique(st, return_counts=True))))
+        print("unsolved: agent index in platoon", np.bincount(bad % A, minlength=A).tolist(), " scenarios", len(np.unique(bad // A)),
+              " NaN in z", int(np.isnan(z[bad]).any(1).sum()))
+        x0 = dm.x0.cpu().numpy()
+        print("unsolved x0 (vx, ey, epsi, s) sample", np.round(x0[bad[:6]][:, [0, 3, 4, 6]], 3).tolist())
+        print("solved   x0 (vx, ey, epsi, s) sample", np.round(x0[:3][:, [0, 3, 4, 6]], 3).tolist())
 
 
 if __name__ == "__main__":

@@ -100,6 +100,23 @@ def test_reference_startup_case(built, cfg, track):
     _compare(out, o["z"], o["y"], o["obj"], o["planes"], eng.m_in)
 
 
+def test_low_speed_qp_is_not_reported_infeasible(built, cfg, track):
+    """KNOWN GAP, kept as a regression fixture: a QP of the 16-agent closed loop (scenario 231, agent 3, second DMPC
+    iteration; inputs captured on the GPU by scripts/gpu_find_bad.py, solution = the oracle's certified optimum).  The
+    vehicle crawls (vx 0.57 -> 0.22 over the horizon) where the forward-Euler lateral dynamics of _EstimateABC are
+    unstable (|1 - dt (Cf+Cr)/(m vx)| up to 7): the condensed prediction matrices grow to ~1e11 and the FP64
+    factorisation of the condensed H breaks down in BOTH engines, while the oracle's uncondensed sparse solve is fine.
+    The QP is feasible, so the path must not certify infeasibility (-3): it reports DMPC_UNSOLVED (-10).  When a
+    stage-wise (Riccati) factorisation replaces condensation for such QPs this test starts demanding full parity."""
+    g = golden("closed_loop_ipm_start_qp.npz")
+    for engine in (2, 1):
+        eng = _engine(cfg, track, options={"engine": engine})
+        out = eng.solve_batch_host(**{k: g["in_" + k] for k in INPUT_KEYS})
+        assert out["status"][0] in (1, 2, -10), out["status"]
+        if out["status"][0] == 1:
+            _compare(out, g["out_z"], g["out_y"], g["out_obj"], g["out_planes"], eng.m_in)
+
+
 def test_recorded_reference_run_horizon_125(built, cfg, track):
     """The reference's recorded experiment (LPV3r_agent_laptop, N=125): its first DMPC iteration from the reference's
     cold start through the CUDA path (generic engine, global-memory workspace).  Parity with the oracle's certified
