@@ -52,6 +52,13 @@ class DmpcBatchIO(C.Structure):
     ]
 
 
+class DmpcShiftIO(C.Structure):
+    """dmpc_shift_io: the next DMPC iteration's buffers, written by the solve's own epilogue."""
+    _fields_ = [(k, C.c_void_p) for k in ("x0", "xprev", "uprev", "uold", "xy_send", "hold")]
+
+
+ENGINE_AUTO, ENGINE_FAST, ENGINE_STAGE = 0, 2, 3
+
 # Defaults of PlannerLPV.__init__ when model_param / sys_lim are None (LPV_Planner.py:33-57)
 DEFAULT_MODEL = dict(lf=0.12, lr=0.14, m=2.250, I=0.06, Cf=60.0, Cr=60.0, mu=0.05)
 DEFAULT_LIMITS = dict(vx_ref=6.0, min_dist=0.45, max_vel=5.5, min_vel=0.2, max_rs=0.45, max_ls=0.45,
@@ -104,7 +111,8 @@ def default_lib_path():
 
 
 EXPORTS = ["dmpc_default_options", "dmpc_version", "dmpc_create", "dmpc_destroy", "dmpc_last_error",
-           "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
+           "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_shift_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
+           "dmpc_shift_pack_hold",
            "dmpc_gather_neighbours", "dmpc_launch_count", "dmpc_engine", "dmpc_sim_batch",
            "dmpc_ocd_lambda_update", "dmpc_ocd_lambda_update_hp"]
 
@@ -135,6 +143,10 @@ def load_library(path=None):
     lib.dmpc_set_options.restype = C.c_int
     lib.dmpc_solve_batch.argtypes = [C.c_void_p, C.POINTER(DmpcBatchIO), C.c_void_p]
     lib.dmpc_solve_batch.restype = C.c_int
+    lib.dmpc_solve_shift_batch.argtypes = [C.c_void_p, C.POINTER(DmpcBatchIO), C.POINTER(DmpcShiftIO), C.c_void_p]
+    lib.dmpc_solve_shift_batch.restype = C.c_int
+    lib.dmpc_shift_pack_hold.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 10
+    lib.dmpc_shift_pack_hold.restype = C.c_int
     lib.dmpc_solve_batch_host.argtypes = [C.c_void_p, C.POINTER(DmpcBatchIO)]
     lib.dmpc_solve_batch_host.restype = C.c_int
     lib.dmpc_shift_pack.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 7

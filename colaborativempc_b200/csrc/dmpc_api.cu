@@ -1,23 +1,26 @@
 // dmpc_api.cu - C ABI (include/dmpc_b200.h) over the sm_100a kernels.  No torch types, no CPU compute path:
-// every numeric result comes from lpv_qp_solve_kernel / the bookkeeping kernels below.
+// every numeric result comes from lpv_qp_stage_kernel / lpv_qp_fast_kernel / the bookkeeping kernels below.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
 
-#include "qp_kernel.cuh"
 #include "qp2_kernel.cuh"
+#include "qp3_kernel.cuh"
 #include "lpv_sim.cuh"
+#include "qp_params.h"
 
 struct dmpc_handle {
   dmpc_params params;
   dmpc_options opt;
   DevParams P;
   int device, max_batch, smem_limit;
-  int fast;  // 1: lpv_qp_fast_kernel (qp2_*.cuh), 0: lpv_qp_solve_kernel (generic)
-  size_t smem_bytes;
-  long long gws_stride;
+  int fast;  // 1: lpv_qp_fast_kernel (condensed, qp2_*.cuh), 0: lpv_qp_stage_kernel (stage-wise, qp3_*.cuh)
+  int stage_ok;            // the stage-wise workspace fits in shared memory (always required when !fast)
+  size_t smem_bytes;       // fast engine workspace
+  size_t stage_smem;       // stage-wise workspace
+  long long gws_stride;    // doubles per QP of the stage-wise engine's global scratch (parked interior-point iterate)
   double* d_gws;
   int *d_cost, *d_order;  // fast engine: per-QP cost of the last call and the launch order derived from it
   int order_B;            // batch size d_order is valid for (0: none yet)
@@ -59,13 +62,8 @@ static void apply_options(dmpc_handle* h) {
 
 static bool options_ok(const dmpc_options* o) {
   return o->polish_delta > 0 && o->polish_delta < 1e-3 && o->cert_tol > 0 && o->ipm_mu0 > 0 && o->polish_refine >= 0 &&
-         o->polish_refine <= 32 && o->pdas_first >= 0 && o->pdas_after >= 1 && o->ipm_max_iter >= 1 && o->engine >= 0 &&
-         o->engine <= 2;
+         o->polish_refine <= 32 && o->pdas_first >= 0 && o->pdas_after >= 1 && o->ipm_max_iter >= 1 && (o->engine == DMPC_ENGINE_AUTO || o->engine == DMPC_ENGINE_FAST || o->engine == DMPC_ENGINE_STAGE);
 }
-
-// symmetric matrix as OSQP sees it: the upper triangle of the user's array (LPV_Planner.py:156 hands csr(M), and
-// OSQP reads triu(P)).
-static double sym_up(const double* M, int n, int i, int j) { return i <= j ? M[i * n + j] : M[j * n + i]; }
 
 static bool psd(const double* M, int n, bool strict) {  // LDL' without pivoting on the symmetrised matrix
   double a[81];
@@ -117,69 +115,47 @@ extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_
   h->max_batch = max_batch;
 
   DevParams& P = h->P;
-  P.N = p->N; P.nn = p->nn; P.nseg = p->nseg;
-  P.dt = p->dt; P.wq = p->wq; P.Q00 = p->Q[0];
-  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) P.Qs[i * 3 + j] = sym_up(p->Qs, 3, i, j);
-  for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) { P.R[i * 2 + j] = sym_up(p->R, 2, i, j); P.dR[i * 2 + j] = sym_up(p->dR, 2, i, j); }
-  P.lf = p->lf; P.lr = p->lr; P.m = p->m; P.I = p->I; P.Cf = p->Cf; P.Cr = p->Cr; P.mu = p->mu;
-  P.vx_ref = p->vx_ref; P.min_dist = p->min_dist; P.max_vel = p->max_vel; P.min_vel = p->min_vel;
-  P.max_rs = p->max_rs; P.max_ls = p->max_ls; P.max_ac = p->max_ac; P.max_dc = p->max_dc;
-  for (int i = 0; i < DMPC_MAX_SEG; ++i) { P.seg_s0[i] = p->seg_s0[i]; P.seg_len[i] = p->seg_len[i]; P.seg_curv[i] = p->seg_curv[i]; P.seg_hw[i] = p->seg_hw[i]; }
-  // state rows kept on chip: the four constrained outputs first, then every other state the cost touches
-  int pos[9];
-  for (int a = 0; a < 9; ++a) pos[a] = -1;
-  const int base[4] = {0, 3, 7, 8};
-  P.nrows = 0;
-  for (int i = 0; i < 4; ++i) { pos[base[i]] = P.nrows; P.rowsel[P.nrows++] = base[i]; }
-  for (int a = 0; a < 9; ++a) {
-    bool used = false;
-    for (int b = 0; b < 9; ++b) used |= (sym_up(p->Q, 9, a, b) != 0.0);
-    if (used && pos[a] < 0) { pos[a] = P.nrows; P.rowsel[P.nrows++] = a; }
-  }
-  P.nq = 0;
-  for (int a = 0; a < 9; ++a) for (int b = a; b < 9; ++b) {
-    const double v = sym_up(p->Q, 9, a, b);
-    if (v != 0.0) { P.qa[P.nq] = pos[a]; P.qb[P.nq] = pos[b]; P.qv[P.nq] = v; ++P.nq; }
-  }
-  apply_options(h);
+  fill_dev_params(p, &h->opt, P);
 
-  // workspace placement: shared memory first, long horizons spill the big blocks to an L2-resident global slice
   int optin = 0;
   CUDA_TRY(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
   h->smem_limit = optin;
-  {  // fast engine: the whole packed workspace in shared memory (qp2_engine.cuh)
+  CUDA_TRY(h, cudaDeviceGetAttribute(&h->nsm, cudaDevAttrMultiProcessorCount, device));
+  // stage-wise engine: O(N) workspace per QP in shared memory, the parked interior-point iterate in a global slice
+  {
+    Ctx3 c3;
+    const size_t sb3 = carve_workspace3(c3, nullptr, P.N, P.nn);
+    h->stage_ok = sb3 + 1024 <= (size_t)optin && P.N <= 511 && P.nn <= 123;  // rinfo packs (stage << 7) | row in 16 bits
+    h->stage_smem = sb3;
+  }
+  bool fast_fits = false;
+  size_t sb2 = 0;
+  {  // condensed engine: the whole packed workspace in shared memory (qp2_engine.cuh)
     Ctx2 c2;
-    const size_t sb2 = FAST_HDR_BYTES + carve_workspace2(c2, nullptr, P.N, P.nn, P.nrows);
-    const bool fits = sb2 + 1024 <= (size_t)optin && 2 * P.N <= 255 && P.N <= 4095;
-    if (h->opt.engine == DMPC_ENGINE_FAST && !fits)
-      return fail(h, DMPC_ERR_UNSUPPORTED, "horizon too long for the fast engine%s");
-    if (fits && h->opt.engine != DMPC_ENGINE_GENERIC) {
-      h->fast = 1; h->smem_bytes = sb2; h->gws_stride = 0;
-      CUDA_TRY(h, cudaMalloc(&h->d_cost, sizeof(int) * (size_t)max_batch));
-      CUDA_TRY(h, cudaMalloc(&h->d_order, sizeof(int) * ((size_t)max_batch + 1)));  // [max_batch]: expensive-QP count
-      {
-        CUDA_TRY(h, cudaDeviceGetAttribute(&h->nsm, cudaDevAttrMultiProcessorCount, device));
-        // alone on the SM: a second CTA of this kernel (sb2 + 1 KB system share each) must not fit beside it
-        const size_t per_sm = (size_t)optin + 1024;
-        h->smem_alone = per_sm > 2 * (sb2 + 1024) ? per_sm - (sb2 + 1024) - 1024 + 16 : sb2;
-        if (h->smem_alone > (size_t)optin) h->smem_alone = (size_t)optin;
-        if (h->smem_alone < sb2) h->smem_alone = sb2;
-        CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_alone));
-      }
-      return DMPC_OK;
-    }
+    sb2 = FAST_HDR_BYTES + carve_workspace2(c2, nullptr, P.N, P.nn, P.nrows);
+    fast_fits = sb2 + 1024 <= (size_t)optin && 2 * P.N <= 255 && P.N <= 4095;
   }
-  Ctx c;
-  bool placed = false;
-  for (int mode = 0; mode < 3 && !placed; ++mode) {
-    P.gr_global = mode >= 1; P.hk_global = mode >= 2;
-    long long gd = 0;
-    const size_t sb = carve_workspace(c, nullptr, nullptr, P.N, P.nn, P.nrows, P.gr_global, P.hk_global, &gd);
-    if (sb + 64 <= (size_t)optin) { h->smem_bytes = sb + 16; h->gws_stride = (gd + 1) & ~1LL; placed = true; }
+  if (h->opt.engine == DMPC_ENGINE_FAST && !fast_fits)
+    return fail(h, DMPC_ERR_UNSUPPORTED, "horizon too long for the condensed engine%s");
+  h->fast = h->opt.engine == DMPC_ENGINE_FAST;
+  if (!h->fast && !h->stage_ok)
+    return fail(h, DMPC_ERR_UNSUPPORTED, "horizon/neighbour count too large for the on-chip workspace%s");
+  if (h->stage_ok) {
+    h->gws_stride = (long long)((stage_park_doubles(P.N, P.nn) + 1) & ~(size_t)1);
+    CUDA_TRY(h, cudaMalloc(&h->d_gws, (size_t)h->gws_stride * sizeof(double) * max_batch));
+    CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->stage_smem));
   }
-  if (!placed) return fail(h, DMPC_ERR_UNSUPPORTED, "horizon/neighbour count too large for the on-chip workspace%s");
-  if (h->gws_stride > 0) CUDA_TRY(h, cudaMalloc(&h->d_gws, (size_t)h->gws_stride * sizeof(double) * max_batch));
-  CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+  if (h->fast) {
+    h->smem_bytes = sb2;
+    CUDA_TRY(h, cudaMalloc(&h->d_cost, sizeof(int) * (size_t)max_batch));
+    CUDA_TRY(h, cudaMalloc(&h->d_order, sizeof(int) * ((size_t)max_batch + 1)));  // [max_batch]: expensive-QP count
+    // alone on the SM: a second CTA of this kernel (sb2 + 1 KB system share each) must not fit beside it
+    const size_t per_sm = (size_t)optin + 1024;
+    h->smem_alone = per_sm > 2 * (sb2 + 1024) ? per_sm - (sb2 + 1024) - 1024 + 16 : sb2;
+    if (h->smem_alone > (size_t)optin) h->smem_alone = (size_t)optin;
+    if (h->smem_alone < sb2) h->smem_alone = sb2;
+    CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_alone));
+  }
   return DMPC_OK;
 }
 
@@ -204,39 +180,54 @@ extern "C" int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt) {
   return DMPC_OK;
 }
 
-extern "C" int dmpc_engine(const dmpc_handle* h) { return h ? (h->fast ? DMPC_ENGINE_FAST : DMPC_ENGINE_GENERIC) : 0; }
+extern "C" int dmpc_engine(const dmpc_handle* h) { return h ? (h->fast ? DMPC_ENGINE_FAST : DMPC_ENGINE_STAGE) : 0; }
 
 extern "C" int64_t dmpc_launch_count(const dmpc_handle* h) { return h ? h->launches : 0; }
 
-extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* stream) {
+static int launch_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, const int32_t* d_status, double* d_x0,
+                             double* d_xprev, double* d_uprev, double* d_uold, double* d_xy_send, int32_t* d_hold, void* stream);
+
+// One batch: the solve and, with `next`, the caller's bookkeeping.  Stage-wise engine: one launch does both.
+// Condensed engine: its (split) launch, then the stage-wise kernel over the QPs it reported DMPC_UNSOLVED (numerical
+// breakdown of the condensed factorisation - crawling vehicles), then the shift kernel.
+static int solve_impl(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_io* next, void* stream) {
   if (!h || !io) return DMPC_ERR_ARG;
   if (io->B == 0) return DMPC_OK;
   if (io->B < 0 || io->B > h->max_batch) return fail(h, DMPC_ERR_ARG, "batch larger than max_batch%s");
   if (io->xprev_rows < h->P.N) return fail(h, DMPC_ERR_ARG, "Last_xPredicted needs at least N rows%s");
   if (!io->x0 || !io->xprev || !io->uprev || !io->uold || !io->pose || (h->P.nn > 0 && !io->nbr_xy))
     return fail(h, DMPC_ERR_ARG, "null input pointer%s");
+  if (next && (!next->x0 || !next->xprev || !next->uprev || !next->uold || !next->xy_send || !next->hold))
+    return fail(h, DMPC_ERR_ARG, "dmpc_shift_io: all six buffers are required%s");
+  if (next && (!io->z || !io->status) && h->fast) return fail(h, DMPC_ERR_ARG, "the condensed engine shifts from z and status%s");
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  cudaStream_t st = (cudaStream_t)stream;
   BatchPtrs bp;
+  memset(&bp, 0, sizeof(bp));
   bp.B = io->B; bp.xprev_rows = io->xprev_rows;
   bp.x0 = io->x0; bp.xprev = io->xprev; bp.uprev = io->uprev; bp.uold = io->uold; bp.nbr_xy = io->nbr_xy; bp.pose = io->pose;
   bp.nbr_count = io->nbr_count;
   bp.z = io->z; bp.planes = io->planes; bp.y_ineq = io->y_ineq; bp.y_eq = io->y_eq; bp.obj = io->obj;
   bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
   bp.gws = h->d_gws; bp.gws_stride = h->gws_stride;
-  bp.order = nullptr; bp.cost = nullptr;
-  if (h->fast) {
+  if (!h->fast) {
+    if (next) { bp.nx_x0 = next->x0; bp.nx_xprev = next->xprev; bp.nx_uprev = next->uprev; bp.nx_uold = next->uold; bp.nx_xy = next->xy_send; bp.hold = next->hold; }
+    lpv_qp_stage_kernel<<<io->B, QP3_THREADS, h->stage_smem, st>>>(h->P, bp);
+    h->launches++;
+    CUDA_TRY(h, cudaGetLastError());
+    return DMPC_OK;
+  }
+  {
     // cost-ordered launch (dmpc_options.order_hint): this call starts its QPs in decreasing order of what the previous
     // call of the same batch size spent on them - consecutive MPC steps of a scenario are alike, so the few
     // interior-point QPs start first instead of becoming the tail of the grid.  Scheduling only; results do not change.
     const bool hint = h->opt.order_hint != 0;
-    bp.nhard = nullptr; bp.part = 0;
     if (hint) { bp.cost = h->d_cost; if (h->order_B == io->B) bp.order = h->d_order; }
     if (bp.order && h->smem_alone > h->smem_bytes) {
-      // The QPs that needed the interior-point phase last time (order[0 .. nhard), ~1 %, ~1.6 ms each alone but 2.2 ms
-      // when two other CTAs share the SM) are launched first with a shared-memory request that keeps each of them alone
-      // on an SM; the bulk follows in the same stream as a programmatic dependent launch: it may start as soon as every
-      // CTA of the first part is resident (they signal at entry), so it fills the other SMs and never has to be waited
-      // for by a CTA that needs a whole SM.  Same kernel, same arithmetic per QP.
-      cudaStream_t st = (cudaStream_t)stream;
+      // The QPs that needed the interior-point phase last time (order[0 .. nhard), ~1 %) are launched first with a
+      // shared-memory request that keeps each of them alone on an SM; the bulk follows in the same stream as a
+      // programmatic dependent launch: it may start as soon as every CTA of the first part is resident (they signal at
+      // entry), so it fills the other SMs.  Same kernel, same arithmetic per QP.
       bp.nhard = h->d_order + h->max_batch;
       bp.part = 1;
       lpv_qp_fast_kernel<<<io->B < h->nsm ? io->B : h->nsm, QP_THREADS, h->smem_alone, st>>>(h->P, bp);
@@ -251,19 +242,33 @@ extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* s
       CUDA_TRY(h, cudaLaunchKernelEx(&cfg, lpv_qp_fast_kernel, h->P, bp));
       h->launches++;
     } else {
-      lpv_qp_fast_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+      lpv_qp_fast_kernel<<<io->B, QP_THREADS, h->smem_bytes, st>>>(h->P, bp);
     }
+    h->launches++;
     if (hint) {
-      order_by_cost_kernel<<<1, ORDER_THREADS, 0, (cudaStream_t)stream>>>(h->d_cost, h->d_order, h->d_order + h->max_batch, io->B, h->nsm);
+      order_by_cost_kernel<<<1, ORDER_THREADS, 0, st>>>(h->d_cost, h->d_order, h->d_order + h->max_batch, io->B, h->nsm);
       h->order_B = io->B;
       h->launches++;
     }
-  } else {
-    lpv_qp_solve_kernel<<<io->B, QP_THREADS, h->smem_bytes, (cudaStream_t)stream>>>(h->P, bp);
+    if (h->stage_ok && io->status) {  // what the condensed factorisation could not handle is solved stage-wise
+      bp.order = nullptr; bp.cost = nullptr; bp.nhard = nullptr; bp.part = 0;
+      bp.only_status = DMPC_UNSOLVED;
+      lpv_qp_stage_kernel<<<io->B, QP3_THREADS, h->stage_smem, st>>>(h->P, bp);
+      h->launches++;
+    }
   }
-  h->launches++;
   CUDA_TRY(h, cudaGetLastError());
+  if (next)
+    return launch_shift_pack(h, io->B, io->z, io->status, next->x0, next->xprev, next->uprev, next->uold, next->xy_send,
+                             next->hold, stream);
   return DMPC_OK;
+}
+
+extern "C" int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* stream) { return solve_impl(h, io, nullptr, stream); }
+
+extern "C" int dmpc_solve_shift_batch(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_io* next, void* stream) {
+  if (!next) return h ? fail(h, DMPC_ERR_ARG, "null dmpc_shift_io%s") : DMPC_ERR_ARG;
+  return solve_impl(h, io, next, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -363,12 +368,21 @@ extern "C" int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io) {
 
 // ---------------------------------------------------------------------------------------------------
 // DMPC bookkeeping kernels (planner/scripts/LPV_HP_N_main.py:106,113-117; LPV_Planner.py:179-180).
-__global__ void shift_pack_kernel(int B, int N, const double* __restrict__ z, double* __restrict__ x0, double* __restrict__ xprev,
-                                  double* __restrict__ uprev, double* __restrict__ uold, double* __restrict__ xy) {
+// status != nullptr: the reference's stop rule (LPV_HP_N_main.py:102-104) - a QP whose solve was not feasible
+// (LPV_Planner.py:246-248) keeps all its buffers (last valid plan) and its hold counter goes up; feasible resets it.
+__global__ void shift_pack_kernel(int B, int N, const double* __restrict__ z, const int* __restrict__ status,
+                                  double* __restrict__ x0, double* __restrict__ xprev, double* __restrict__ uprev,
+                                  double* __restrict__ uold, double* __restrict__ xy, int* __restrict__ hold) {
   const int n = 16 * N + 12;
   const long long total = (long long)B * n;
   for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
     const int b = (int)(w / n), j = (int)(w % n);
+    if (status) {
+      const int st = status[b];
+      const bool feas = st == DMPC_SOLVED || st == DMPC_SOLVED_INACCURATE || st == DMPC_MAX_ITER_REACHED;
+      if (j == 0 && hold) hold[b] = feas ? 0 : hold[b] + 1;
+      if (!feas) continue;
+    }
     const double v = z[w];
     if (j < 12 * (N + 1)) {
       const int t = j / 12, r = j % 12;
@@ -481,16 +495,28 @@ extern "C" int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, 
   return DMPC_OK;
 }
 
-extern "C" int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, double* d_x0, double* d_xprev, double* d_uprev,
-                               double* d_uold, double* d_xy_send, void* stream) {
+static int launch_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, const int32_t* d_status, double* d_x0,
+                             double* d_xprev, double* d_uprev, double* d_uold, double* d_xy_send, int32_t* d_hold, void* stream) {
   if (!h || !d_z || B < 0) return DMPC_ERR_ARG;
   if (B == 0) return DMPC_OK;
   const long long total = (long long)B * (16 * h->P.N + 12);
   const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-  shift_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(B, h->P.N, d_z, d_x0, d_xprev, d_uprev, d_uold, d_xy_send);
+  shift_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(B, h->P.N, d_z, d_status, d_x0, d_xprev, d_uprev, d_uold, d_xy_send, d_hold);
   h->launches++;
   CUDA_TRY(h, cudaGetLastError());
   return DMPC_OK;
+}
+
+extern "C" int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, double* d_x0, double* d_xprev, double* d_uprev,
+                               double* d_uold, double* d_xy_send, void* stream) {
+  return launch_shift_pack(h, B, d_z, nullptr, d_x0, d_xprev, d_uprev, d_uold, d_xy_send, nullptr, stream);
+}
+
+extern "C" int dmpc_shift_pack_hold(dmpc_handle* h, int32_t B, const double* d_z, const int32_t* d_status, double* d_x0,
+                                    double* d_xprev, double* d_uprev, double* d_uold, double* d_xy_send, int32_t* d_hold,
+                                    void* stream) {
+  if (!d_status || !d_hold) return h ? fail(h, DMPC_ERR_ARG, "dmpc_shift_pack_hold needs status and hold%s") : DMPC_ERR_ARG;
+  return launch_shift_pack(h, B, d_z, d_status, d_x0, d_xprev, d_uprev, d_uold, d_xy_send, d_hold, stream);
 }
 
 // xy_all is laid out as ncclAllGather leaves it: [G][S][A_local][T][2] with G = A_total / A_local ranks, i.e. global

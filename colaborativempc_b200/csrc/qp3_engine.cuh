@@ -1,0 +1,771 @@
+// qp3_engine.cuh - STAGE-WISE engine: the LPV-MPC QP of PlannerLPV.solve solved in its UNCONDENSED form, the way the
+// reference hands it to OSQP (distributedPlanner/LPV_Planner.py:222-239: states, slacks, inputs and input increments are
+// all variables, the dynamics are equality rows), with every linear solve done by a Riccati recursion over the stages.
+//
+// Why: condensing (qp2_*.cuh) multiplies the A_k along the horizon; for crawling vehicles the forward-Euler lateral
+// dynamics of _EstimateABC (LPV_Planner.py:505-517) are unstable (|1 - dt (Cf+Cr)/(m vx)| up to 7), the products reach
+// 1e11+ and the condensed Hessian cannot be factorised in FP64.  The stage-wise factorisation never forms a product of
+// two A_k: it carries the cost-to-go  V_k(xi) = 1/2 xi' P_k xi + p_k' xi  backwards (closed loop, bounded) and the state
+// forwards under the optimal feedback.  Memory and work are O(N): ~190 doubles per stage, so N = 125 (the reference's
+// shipped horizon, config_files/config_LPV.py:24) still fits in one SM's shared memory.
+//
+// One WARP per QP.  The recursion is sequential over the stages; inside a stage the 11 x 11 cost-to-go update is spread
+// over the 32 lanes (three phases, __syncwarp between them).  Everything that has no stage-to-stage dependence (rows,
+// slack elimination, gradients, step lengths) runs with one lane per stage or per row.
+//
+// Variables, per stage k = 0 .. N-1:  u_k (2),  x_{k+1} (9),  sigma_{k+1} (3).  Augmented state xi_k = (x_k, v_k = u_{k-1})
+// carries the input-increment cost (u_k - u_{k-1})' dR (u_k - u_{k-1}) of LPV_Planner.py:404-409 without du variables.
+// Rows (LPV_Planner.py:304-369), stage k on (x_{k+1}, sigma_{k+1}):  r0 -vx <= -min_vel,  r1 vx + s0 <= max_vel,
+// r2 e_y + s1 <= ey,  r3 -e_y + s1 <= ey,  r4+i  a_i . (x,y) - s2 <= -min_dist/2 - b_i;   box rows on u_k (4).
+//
+// The same source compiles for the host (QP3_HOST: one "lane", no barriers) so that the algorithm can be checked in the
+// CPU-only test tier (tests/hostsim, test infrastructure); the product only ever runs the sm_100a kernel.
+#pragma once
+#include <math.h>
+
+#include "qp_types.h"
+
+#ifdef QP3_HOST
+#define Q3HD inline
+#define Q3D static inline
+#define Q3N static
+#define Q3_NL 1
+#define Q3_LANE 0
+#define Q3_SYNC() ((void)0)
+static inline double q3_wsum(double v) { return v; }
+static inline double q3_wmax(double v) { return v; }
+static inline double q3_wmin(double v) { return v; }
+static inline int q3_wor(int v) { return v; }
+static inline unsigned long long q3_wsum64(unsigned long long v) { return v; }
+static thread_local char* q3_host_smem = nullptr;
+#define Q3_SMEM q3_host_smem
+#else
+#include <cuda_runtime.h>
+#define Q3HD __host__ __device__ inline
+#define Q3D __device__ __forceinline__
+#define Q3N __device__ __noinline__
+#define Q3_NL 32
+#define Q3_LANE ((int)(threadIdx.x & 31))
+#define Q3_SYNC() __syncwarp()
+__device__ __forceinline__ double q3_wsum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double q3_wmax(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double q3_wmin(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ int q3_wor(int v) { return __any_sync(0xffffffffu, v); }
+__device__ __forceinline__ unsigned long long q3_wsum64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+extern __shared__ __align__(16) char smem_stage[];
+#define Q3_SMEM smem_stage
+#endif
+
+// lane-strided item loop: on the device the 32 lanes share the items, on the host one "lane" walks them all
+#define Q3_FOR(i, n) for (int i = Q3_LANE; i < (n); i += Q3_NL)
+
+// Header at the start of the workspace: sizes, options, the cost / limit constants and the small Riccati scratch.
+struct Hdr3 {
+  int N, nn, cnt, rows;
+  int refine, pdas_first, pdas_after, ipm_max;
+  int n_rounds, n_ipm, n_fact, n_solve;
+  double delta, cert_tol, ipm_mu0;
+  double Q2[81];      // 2 Q   (P = 2 blockdiag(...), LPV_Planner.py:399-410)
+  double Qs2[9];      // 2 Qs
+  double R2[4], dR2[4];
+  double q0;          // 2 * (-vx_ref Q[0,0])   (LPV_Planner.py:412)
+  double lim[6];      // min_vel max_vel max_rs max_ls max_ac max_dc
+  double mind;        // min_dist
+  double x0[9], uold[2];
+  // cost-to-go and the per-stage temporaries of the Riccati passes
+  double Pxx[81], Pvx[18], Pvv[4], px[2][9], pv[2][2];
+  double MA[27], G[18], ev[9], fv[2], TA[9], Fs[6], Huu[4], hu[2], Apx[9];
+  double fx[2][9], fu[2][2];   // forward sweep: the step of the running stage (ping-pong)
+  unsigned long long hist[16];
+  unsigned char tri[48];  // (i << 4) | j of the 45 upper-triangle pairs of a 9 x 9 matrix
+};
+
+struct Ctx3 {
+  int N, nn, cnt, rst, Rs, RT;
+  Hdr3* hd;
+  double *Acol, *Bcol, *ax, *ay, *mx, *my, *eyb, *pxy;   // problem data (mx, my: midpoint ego-neighbour, on the plane)
+  double *x, *u, *sig, *lam, *tt;                         // iterate: x[k] = x_{k+1}
+  double *dx, *du, *dsig, *dlam, *dtt;                    // direction (dx doubles as the dynamics defect on input)
+  double *gx, *gu, *gs;                                   // gradient handed to a solve
+  double *D, *res;                                        // row weights, row residuals
+  double *F, *Wi, *zk, *Si, *bh, *Weff;                   // Riccati factor per stage, slack elimination per stage
+  unsigned short* rinfo;                                  // row j -> (k << 7) | r
+  unsigned char* act;
+};
+
+#define Q3_HDR_BYTES ((sizeof(Hdr3) + 15) & ~(size_t)15)
+
+// doubles per QP after the header
+Q3HD size_t carve_workspace3(Ctx3& c, char* sm, int N, int nn) {
+  c.N = N; c.nn = nn; c.rst = 4 + nn; c.Rs = N * c.rst; c.RT = c.Rs + 4 * N;
+  c.hd = (Hdr3*)sm;
+  double* p = (double*)(sm + Q3_HDR_BYTES);
+  auto take = [&](size_t n) { double* r = p; p += n; return r; };
+  const size_t n = (size_t)N, RT = (size_t)c.RT;
+  c.Acol = take(27 * n); c.Bcol = take(4 * n);
+  c.ax = take(n * nn); c.ay = take(n * nn); c.mx = take(n * nn); c.my = take(n * nn);
+  c.eyb = take(n); c.pxy = take(2 * n);
+  c.x = take(9 * n); c.u = take(2 * n); c.sig = take(3 * n); c.lam = take(RT); c.tt = take(RT);
+  c.dx = take(9 * n); c.du = take(2 * n); c.dsig = take(3 * n); c.dlam = take(RT); c.dtt = take(RT);
+  c.gx = take(9 * n); c.gu = take(2 * n); c.gs = take(3 * n);
+  c.D = take(RT); c.res = take(RT);
+  c.F = take(18 * n); c.Wi = take(4 * n); c.zk = take(2 * n);
+  c.Si = take(6 * n); c.bh = take(4 * n); c.Weff = take(10 * n);
+  c.rinfo = (unsigned short*)take((RT + 3) / 4);
+  c.act = (unsigned char*)take((RT + 7) / 8);
+  return (size_t)((char*)p - sm);
+}
+
+// doubles the IPM iterate occupies when parked in the global scratch slice of a QP (x, u, sigma, lambda, t)
+Q3HD size_t stage_park_doubles(int N, int nn) { return (size_t)14 * N + 2 * (size_t)N * (8 + nn); }
+
+#define Q3_CTX(c)                                              \
+  Ctx3 c;                                                      \
+  {                                                            \
+    const Hdr3* h_ = (const Hdr3*)Q3_SMEM;                     \
+    carve_workspace3(c, Q3_SMEM, h_->N, h_->nn);               \
+    c.cnt = h_->cnt;                                           \
+  }
+
+// ---------------------------------------------------------------------------------------------------
+// rows
+Q3D bool row_ok3(const Ctx3& c, int j) { return j >= c.Rs || (c.rinfo[j] & 127) < 4 + c.cnt; }
+
+Q3D double row_b3(const Ctx3& c, int j) {
+  const int ri = c.rinfo[j], r = ri & 127, k = ri >> 7;
+  const double* lim = c.hd->lim;
+  if (j >= c.Rs) return lim[2 + r];
+  if (r == 0) return -lim[0];
+  if (r == 1) return lim[1];
+  if (r < 4) return c.eyb[k];
+  const int i = k * c.nn + (r - 4);
+  return fma(c.ax[i], c.mx[i], c.ay[i] * c.my[i]) - 0.5 * c.hd->mind;  // -min_dist/2 - b, b = -a.m (compute_plane.py:54)
+}
+
+// (A v)_j for states xs (x_{k+1} at 9k), slacks sg, inputs uv
+Q3D double row_val3(const Ctx3& c, int j, const double* xs, const double* sg, const double* uv) {
+  const int ri = c.rinfo[j], r = ri & 127, k = ri >> 7;
+  if (j >= c.Rs) {
+    const double v = uv[2 * k + (r >> 1)];
+    return (r & 1) ? -v : v;
+  }
+  const double* xk = xs + 9 * k;
+  const double* sk = sg + 3 * k;
+  if (r == 0) return -xk[0];
+  if (r == 1) return xk[0] + sk[0];
+  if (r == 2) return xk[3] + sk[1];
+  if (r == 3) return -xk[3] + sk[1];
+  return c.ax[k * c.nn + (r - 4)] * xk[7] + c.ay[k * c.nn + (r - 4)] * xk[8] - sk[2];
+}
+
+Q3D void build_tables3(const Ctx3& c) {
+  Q3_FOR(j, c.RT) {
+    int k, r;
+    if (j < c.Rs) { k = j / c.rst; r = j - k * c.rst; } else { k = (j - c.Rs) >> 2; r = (j - c.Rs) & 3; }
+    c.rinfo[j] = (unsigned short)((k << 7) | r);
+  }
+  Q3_FOR(e, 45) {
+    int i = 0, rem = e;
+    while (rem >= 9 - i) { rem -= 9 - i; ++i; }
+    c.hd->tri[e] = (unsigned char)((i << 4) | (i + rem));
+  }
+}
+
+// (A z)_j - b_j at the current iterate, evaluated so that the terms that cancel on an active row are subtracted first
+// (state minus its bound is exact by Sterbenz when the row is tight; collision rows are taken relative to the plane's
+// own point, the ego-neighbour midpoint): the rounding of an active row's residual is then far below an ulp of the
+// state, which is what the multiplier iteration (penalty x residual) amplifies.
+Q3D double row_res3(const Ctx3& c, int j) {
+  const int ri = c.rinfo[j], r = ri & 127, k = ri >> 7;
+  const double* lim = c.hd->lim;
+  if (j >= c.Rs) {
+    const double v = c.u[2 * k + (r >> 1)];
+    return (r & 1) ? -v - lim[2 + r] : v - lim[2 + r];
+  }
+  const double* xk = c.x + 9 * k;
+  const double* sk = c.sig + 3 * k;
+  if (r == 0) return lim[0] - xk[0];
+  if (r == 1) return (xk[0] - lim[1]) + sk[0];
+  if (r == 2) return (xk[3] - c.eyb[k]) + sk[1];
+  if (r == 3) return (-xk[3] - c.eyb[k]) + sk[1];
+  const int i = k * c.nn + (r - 4);
+  return fma(c.ax[i], xk[7] - c.mx[i], c.ay[i] * (xk[8] - c.my[i])) + (0.5 * c.hd->mind - sk[2]);
+}
+
+// res_j at the current iterate; invalid rows (unused neighbour slots) read -1.
+Q3D void eval_residuals3(const Ctx3& c) {
+  Q3_FOR(j, c.RT) c.res[j] = row_ok3(c, j) ? row_res3(c, j) : -1.0;
+  Q3_SYNC();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Track lookup with the semantics of utilities/misc.py:78-101 / :105-126: wrap while s > L, clamp s < 0, segment i with
+// s0[i] <= s < s0[i]+len[i]; -1 where the reference's int(np.where(...)) raises.  The wrap is one floor-based reduction
+// plus a fix-up that keeps the reference's s == k L behaviour (a multiple of L stays at L, where no segment matches).
+Q3D int map_segment3(const DevParams& P, double s) {
+  const double L = P.seg_s0[P.nseg - 1] + P.seg_len[P.nseg - 1];
+  if (!(s == s) || !(L > 0.0) || fabs(s) > 1e6 * L) return -1;
+  if (s > L) {
+    s -= L * floor(s / L);
+    if (s <= 0.0) s += L;   // the reference's loop stops at the first value <= L: exact multiples end at L
+    while (s > L) s -= L;
+  }
+  if (s < 0.0) s = 0.0;
+  int found = -1, cnt = 0;
+  for (int i = 0; i < P.nseg; ++i)
+    if (s >= P.seg_s0[i] && s < P.seg_s0[i] + P.seg_len[i]) { found = i; ++cnt; }
+  return cnt == 1 ? found : -1;
+}
+
+// planes (N,3,nn) (planes/compute_plane.py:41-68, keep_sign=True) + distance weights (utilities/misc.py:10-18) folded
+// into the linear cost of x,y (LPV_Planner.py:416-422).  Nonzero if ego and a neighbour coincide.
+Q3D int setup_planes3(const Ctx3& c, const DevParams& P, const double* nbr, const double* pose, double* planes_out) {
+  int bad = 0;
+  Q3_FOR(h, c.N) {
+    const double ex = pose[2 * h], ey = pose[2 * h + 1];
+    const double fx = pose[2 * (h + 1)], fy = pose[2 * (h + 1) + 1];
+    double sx = 0.0, sy = 0.0;
+    for (int n = 0; n < c.nn; ++n) {
+      double ax = 0.0, ay = 0.0, bb = 0.0;
+      if (n < c.cnt) {
+        const double gx = nbr[(h * c.nn + n) * 2], gy = nbr[(h * c.nn + n) * 2 + 1];
+        ax = gx - ex; ay = gy - ey;
+        const double nrm = sqrt(ax * ax + ay * ay);
+        if (!(nrm > 0.0)) bad = 1;
+        ax /= nrm; ay /= nrm;
+        bb = -0.5 * (ax * (ex + gx) + ay * (ey + gy));
+        const double dx = fx - nbr[((h + 1) * c.nn + n) * 2], dy = fy - nbr[((h + 1) * c.nn + n) * 2 + 1];
+        const double w = (2.0 * P.min_dist - sqrt(dx * dx + dy * dy)) / (double)c.cnt;  // rows 1..N (misc.py:15)
+        sx = fma(w, ax, sx); sy = fma(w, ay, sy);
+      }
+      c.ax[h * c.nn + n] = ax; c.ay[h * c.nn + n] = ay;
+      c.mx[h * c.nn + n] = n < c.cnt ? 0.5 * (ex + nbr[(h * c.nn + n) * 2]) : 0.0;
+      c.my[h * c.nn + n] = n < c.cnt ? 0.5 * (ey + nbr[(h * c.nn + n) * 2 + 1]) : 0.0;
+      if (planes_out) {
+        planes_out[(h * 3 + 0) * c.nn + n] = ax;
+        planes_out[(h * 3 + 1) * c.nn + n] = ay;
+        planes_out[(h * 3 + 2) * c.nn + n] = bb;
+      }
+    }
+    c.pxy[2 * h] = P.wq * sx; c.pxy[2 * h + 1] = P.wq * sy;
+  }
+  return bad;
+}
+
+// A_k = I + dt Ac, B_k = dt Bc along the previous prediction (LPV_Planner.py:491-589); A_k stored as its 9 x 3 column
+// block (only columns 0-2 of Ac are non-zero).  Nonzero on a failed map lookup.
+Q3D int setup_linearise3(const Ctx3& c, const DevParams& P, const double* xprev, int rows, const double* uprev) {
+  int bad = 0;
+  const int nk = c.N > rows ? c.N : rows;
+  Q3_FOR(k, nk) {
+    if (k >= c.N) {  // get_ey is evaluated on every row of Last_xPredicted (LPV_Planner.py:489)
+      if (map_segment3(P, xprev[k * NSTATE + 6]) < 0) bad = 1;
+      continue;
+    }
+    const int re = k < rows ? k : rows - 1;
+    const int sege = map_segment3(P, xprev[re * NSTATE + 6]);
+    const double* x = xprev + k * NSTATE;
+    const double vx = x[0], vy = x[1], ey = x[3], epsi = x[4], theta = x[5];
+    const int seg = map_segment3(P, x[6]);
+    if (seg < 0 || sege < 0) { bad = 1; continue; }
+    c.eyb[k] = P.seg_hw[sege];  // get_ey's own sm=1.0; the controller's sm is never applied (misc.py:105)
+    const double cur = P.seg_curv[seg];
+    const double delta = uprev[2 * k];
+    double sd, cd, se, ce, st, ct;
+    sincos(delta, &sd, &cd); sincos(epsi, &se, &ce); sincos(theta, &st, &ct);
+    double A12 = 0, A13 = 0, A22 = 0, A23 = 0, A32 = 0, A33 = 0, B11 = 0;
+    if (!(vx < 0.2)) {
+      A12 = (sd * P.Cf) / (P.m * vx);
+      A13 = (sd * P.Cf * P.lf) / (P.m * vx) + vy;
+      A22 = -(P.Cr + P.Cf * cd) / (P.m * vx);
+      A23 = -(P.lf * P.Cf * cd - P.lr * P.Cr) / (P.m * vx) - vx;
+      A32 = -(P.lf * P.Cf * cd - P.lr * P.Cr) / (P.I * vx);
+      A33 = -(P.lf * P.lf * P.Cf * cd + P.lr * P.lr * P.Cr) / (P.I * vx);
+      B11 = -(sd * P.Cf) / P.m;
+    }
+    const double den = 1.0 - ey * cur;
+    const double iden = 1.0 / den;
+    const double Ac[27] = {-P.mu, A12, A13,
+                           0.0, A22, A23,
+                           0.0, A32, A33,
+                           se, ce, 0.0,
+                           iden * (-ce * cur), iden * (se * cur), 1.0,
+                           0.0, 0.0, 1.0,
+                           ce / den, -se / den, 0.0,
+                           ct, -st, 0.0,
+                           st, ct, 0.0};
+    double* A = c.Acol + 27 * k;
+    for (int r = 0; r < 9; ++r)
+      for (int j = 0; j < 3; ++j) A[r * 3 + j] = (r == j ? 1.0 : 0.0) + P.dt * Ac[r * 3 + j];
+    double* B = c.Bcol + 4 * k;
+    B[0] = P.dt * B11;
+    B[1] = P.dt * ((cd * P.Cf) / P.m);
+    B[2] = P.dt * ((P.lf * P.Cf * cd) / P.I);
+    B[3] = P.dt;
+  }
+  return bad;
+}
+
+// y = A_k v for the 9 x 9 A_k = [Acol | e_3 .. e_8], row j
+Q3D double arow3(const double* A, const double* v, int j) {
+  double s = j >= 3 ? v[j] : 0.0;
+  s = fma(A[j * 3 + 0], v[0], s); s = fma(A[j * 3 + 1], v[1], s); s = fma(A[j * 3 + 2], v[2], s);
+  return s;
+}
+// (B_k du)_j
+Q3D double brow3(const double* B, double d0, double d1, int j) {
+  return j == 0 ? fma(B[0], d0, B[3] * d1) : (j == 1 ? B[1] * d0 : (j == 2 ? B[2] * d0 : 0.0));
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Per-stage slack elimination for the row weights D: Si = (2Qs + E'DE)^-1 (3x3 symmetric: 00 01 02 11 12 22),
+// bh = E'D C restricted to the outputs (vx, e_y, x, y), Weff = C'DC - bh Si bh' (4x4 symmetric: 00 01 02 03 11 12 13 22
+// 23 33) = what the stage rows add to the Hessian of (vx, e_y, x, y)_{k+1} once the slacks are minimised out.
+Q3D void stage_weights3(const Ctx3& c) {
+  const double* Qs2 = c.hd->Qs2;
+  Q3_FOR(t, c.N) {
+    const double* d = c.D + t * c.rst;
+    double sxx = 0, sxy = 0, syy = 0, sx = 0, sy = 0, sd = 0;
+    for (int i = 0; i < c.cnt; ++i) {
+      const double di = d[4 + i], x = c.ax[t * c.nn + i], y = c.ay[t * c.nn + i];
+      sxx = fma(di * x, x, sxx); sxy = fma(di * x, y, sxy); syy = fma(di * y, y, syy);
+      sx = fma(di, x, sx); sy = fma(di, y, sy); sd += di;
+    }
+    const double b0 = d[1], b1 = d[2] - d[3], b2 = -sx, b3 = -sy;
+    const double s00 = Qs2[0] + d[1], s01 = Qs2[1], s02 = Qs2[2];
+    const double s11 = Qs2[4] + d[2] + d[3], s12 = Qs2[5], s22 = Qs2[8] + sd;
+    const double c00 = s11 * s22 - s12 * s12, c01 = s02 * s12 - s01 * s22, c02 = s01 * s12 - s02 * s11;
+    const double c11 = s00 * s22 - s02 * s02, c12 = s01 * s02 - s00 * s12, c22 = s00 * s11 - s01 * s01;
+    const double idet = 1.0 / (s00 * c00 + s01 * c01 + s02 * c02);
+    double* si = c.Si + 6 * t;
+    si[0] = c00 * idet; si[1] = c01 * idet; si[2] = c02 * idet; si[3] = c11 * idet; si[4] = c12 * idet; si[5] = c22 * idet;
+    double* bh = c.bh + 4 * t;
+    bh[0] = b0; bh[1] = b1; bh[2] = b2; bh[3] = b3;
+    double* w = c.Weff + 10 * t;
+    w[0] = d[0] + d[1] - b0 * b0 * si[0];
+    w[1] = -b0 * b1 * si[1];
+    w[2] = -b0 * b2 * si[2];
+    w[3] = -b0 * b3 * si[2];
+    w[4] = d[2] + d[3] - b1 * b1 * si[3];
+    w[5] = -b1 * b2 * si[4];
+    w[6] = -b1 * b3 * si[4];
+    w[7] = sxx - b2 * b2 * si[5];
+    w[8] = sxy - b2 * b3 * si[5];
+    w[9] = syy - b3 * b3 * si[5];
+  }
+}
+
+// Hessian entry (i, j), i <= j, of the state x_{k+1}: 2Q + S' Weff_k S with S = rows (0, 3, 7, 8)
+Q3D double qt3(const Ctx3& c, int k, int i, int j) {
+  double v = c.hd->Q2[i * 9 + j];
+  const int a = i == 0 ? 0 : (i == 3 ? 1 : (i == 7 ? 2 : (i == 8 ? 3 : -1)));
+  const int b = j == 0 ? 0 : (j == 3 ? 1 : (j == 7 ? 2 : (j == 8 ? 3 : -1)));
+  if (a >= 0 && b >= 0) v += c.Weff[10 * k + a * 4 - ((a * (a - 1)) >> 1) + (b - a)];
+  return v;
+}
+
+// What a solve's gradient is made of.  Always: row term C'w with the per-row w of the mode.
+//   G3_ALM   cost gradient + w = lam + D res              (method-of-multipliers polish pass)
+//   G3_AFF   cost gradient + w = D (res + t)              (interior point, predictor; lam cancels)
+//   G3_COR   w = (smu - dtt dlam) / t only                (interior point, corrector increment; dtt/dlam = affine step)
+//   G3_LAG   cost gradient + w = lam                      (Lagrangian gradient: the costate pass)
+enum { G3_ALM = 0, G3_AFF = 1, G3_COR = 2, G3_LAG = 3 };
+
+Q3D double row_w3(const Ctx3& c, int j, int mode, double smu) {
+  if (mode == G3_ALM) return fma(c.D[j], c.res[j], c.lam[j]);
+  if (mode == G3_AFF) return c.D[j] * (c.res[j] + c.tt[j]);
+  if (mode == G3_COR) return (smu - c.dtt[j] * c.dlam[j]) / c.tt[j];
+  return c.lam[j];
+}
+
+// Gradient of the solve (c.gx, c.gu, c.gs), slack part folded into gx through the stage's Si / bh (stage_weights3 of the
+// current D must have run), and - with `defects` - the dynamics defects d_k = A_k x_k + B_k u_k - x_{k+1} into c.dx
+// (zeros otherwise).  G3_COR is an INCREMENT on top of the predictor: c.gs accumulates (the slack steps are recomputed from
+// the totals) and c.dx keeps the predictor's step.  One lane per stage.  Ends with a barrier.
+Q3D void assemble_gradient3(const Ctx3& c, int mode, double smu, int defects) {
+  const Hdr3* hd = c.hd;
+  Q3_FOR(k, c.N) {
+    const double* xk1 = c.x + 9 * k;
+    const double* sk = c.sig + 3 * k;
+    const double* uk = c.u + 2 * k;
+    const int j0 = k * c.rst, jb = c.Rs + 4 * k;
+    // row terms
+    const double w0 = row_w3(c, j0, mode, smu), w1 = row_w3(c, j0 + 1, mode, smu);
+    const double w2 = row_w3(c, j0 + 2, mode, smu), w3 = row_w3(c, j0 + 3, mode, smu);
+    double wx = 0.0, wy = 0.0, ws = 0.0;
+    for (int i = 0; i < c.cnt; ++i) {
+      const double wi = row_w3(c, j0 + 4 + i, mode, smu);
+      wx = fma(c.ax[k * c.nn + i], wi, wx); wy = fma(c.ay[k * c.nn + i], wi, wy); ws += wi;
+    }
+    double g[9], s[3], gu0, gu1;
+    if (mode == G3_COR) {
+      for (int i = 0; i < 9; ++i) g[i] = 0.0;
+      s[0] = s[1] = s[2] = 0.0; gu0 = gu1 = 0.0;
+    } else {
+      for (int i = 0; i < 9; ++i) {
+        double a = 0.0;
+        for (int l = 0; l < 9; ++l) a = fma(hd->Q2[i * 9 + l], xk1[l], a);
+        g[i] = a;
+      }
+      g[0] += hd->q0;
+      g[7] += 2.0 * c.pxy[2 * k]; g[8] += 2.0 * c.pxy[2 * k + 1];
+      for (int i = 0; i < 3; ++i) s[i] = hd->Qs2[i * 3] * sk[0] + hd->Qs2[i * 3 + 1] * sk[1] + hd->Qs2[i * 3 + 2] * sk[2];
+      const double* um = k > 0 ? uk - 2 : hd->uold;
+      const double d0 = uk[0] - um[0], d1 = uk[1] - um[1];
+      gu0 = hd->R2[0] * uk[0] + hd->R2[1] * uk[1] + hd->dR2[0] * d0 + hd->dR2[1] * d1;
+      gu1 = hd->R2[2] * uk[0] + hd->R2[3] * uk[1] + hd->dR2[2] * d0 + hd->dR2[3] * d1;
+      if (k < c.N - 1) {
+        const double e0 = uk[2] - uk[0], e1 = uk[3] - uk[1];
+        gu0 -= hd->dR2[0] * e0 + hd->dR2[1] * e1;
+        gu1 -= hd->dR2[2] * e0 + hd->dR2[3] * e1;
+      }
+    }
+    g[0] += w1 - w0; g[3] += w2 - w3; g[7] += wx; g[8] += wy;
+    s[0] += w1; s[1] += w2 + w3; s[2] -= ws;
+    gu0 += row_w3(c, jb, mode, smu) - row_w3(c, jb + 1, mode, smu);
+    gu1 += row_w3(c, jb + 2, mode, smu) - row_w3(c, jb + 3, mode, smu);
+    // slack elimination: the slack gradient reaches the outputs as -bh Si gs
+    const double* si = c.Si + 6 * k;
+    const double* bh = c.bh + 4 * k;
+    const double v0 = si[0] * s[0] + si[1] * s[1] + si[2] * s[2];
+    const double v1 = si[1] * s[0] + si[3] * s[1] + si[4] * s[2];
+    const double v2 = si[2] * s[0] + si[4] * s[1] + si[5] * s[2];
+    g[0] -= bh[0] * v0; g[3] -= bh[1] * v1; g[7] -= bh[2] * v2; g[8] -= bh[3] * v2;
+    for (int i = 0; i < 9; ++i) c.gx[9 * k + i] = g[i];
+    if (mode == G3_COR) { c.gs[3 * k] += s[0]; c.gs[3 * k + 1] += s[1]; c.gs[3 * k + 2] += s[2]; }
+    else { c.gs[3 * k] = s[0]; c.gs[3 * k + 1] = s[1]; c.gs[3 * k + 2] = s[2]; }
+    c.gu[2 * k] = gu0; c.gu[2 * k + 1] = gu1;
+    if (mode == G3_COR) continue;
+    if (defects) {
+      const double* xk = k > 0 ? c.x + 9 * (k - 1) : hd->x0;
+      const double* A = c.Acol + 27 * k;
+      const double* B = c.Bcol + 4 * k;
+      for (int i = 0; i < 9; ++i) c.dx[9 * k + i] = arow3(A, xk, i) + brow3(B, uk[0], uk[1], i) - xk1[i];
+    } else {
+      for (int i = 0; i < 9; ++i) c.dx[9 * k + i] = 0.0;
+    }
+  }
+  Q3_SYNC();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Riccati recursion.  Cost-to-go of the augmented state xi = (dx_k, dv_k = du_{k-1}) from stage k on, including the cost
+// of x_k itself:  W_k(xi) = 1/2 xi' [Pxx Pxv; Pvx Pvv] xi + (px, pv)' xi.  Stage k, with P+ = P_{k+1}, defect d_k:
+//   G   = B'Pxx+ + Pvx+                       (2 x 9)         Huu = Rt + dR2 + G B + B'Pxv+ + Pvv+
+//   F   = G A                                 (2 x 9)         hu  = gu + B'(px+ + Pxx+ d) + pv+ + Pvx+ d
+//   du  = -Huu^-1 (hu + F dx - dR2 dv)
+//   Pxx = A'Pxx+A - F'Huu^-1 F + Qt_{k-1}     Pvx = dR2 Huu^-1 F     Pvv = dR2 - dR2 Huu^-1 dR2
+//   px  = A'(px+ + Pxx+ d) - F'Huu^-1 hu + gx_{k-1}               pv  = dR2 Huu^-1 hu
+// A = I + (column block): A'Pxx+A needs MA = Pxx+ Acol (9 x 3) and TA = Acol'MA (3 x 3) only.
+// Kept per stage for later solves with the same weights: F (18), Huu^-1 (3), z = Huu^-1 hu (2).
+// Backward pass with factorisation.  In: c.gx/gu (gradient, slack part folded), c.dx (defects), c.D, c.Weff.
+Q3D void ric_factor_backward3(const Ctx3& c) {
+  Hdr3* hd = c.hd;
+  const int N = c.N;
+  double* Pxx = hd->Pxx;
+  double* Pvx = hd->Pvx;
+  double* Pvv = hd->Pvv;
+  double* px = hd->px[0];
+  double* pv = hd->pv[0];
+  const double* dR2 = hd->dR2;
+  Q3_FOR(e, 45) {
+    const int ij = hd->tri[e], i = ij >> 4, j = ij & 15;
+    const double v = qt3(c, N - 1, i, j);
+    Pxx[i * 9 + j] = v; Pxx[j * 9 + i] = v;
+  }
+  Q3_FOR(e, 18) Pvx[e] = 0.0;
+  Q3_FOR(e, 4) Pvv[e] = 0.0;
+  Q3_FOR(e, 9) px[e] = c.gx[9 * (N - 1) + e];
+  Q3_FOR(e, 2) pv[e] = 0.0;
+  Q3_SYNC();
+#pragma unroll 1
+  for (int k = N - 1; k >= 0; --k) {
+    const double* A = c.Acol + 27 * k;
+    const double* B = c.Bcol + 4 * k;
+    const double* d = c.dx + 9 * k;
+    // ---- phase 1: everything that reads P+ only
+    Q3_FOR(it, 59) {
+      if (it < 27) {
+        const int i = it / 3, j = it - 3 * i;
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int l = 0; l < 8; l += 2) { s0 = fma(Pxx[i * 9 + l], A[l * 3 + j], s0); s1 = fma(Pxx[i * 9 + l + 1], A[(l + 1) * 3 + j], s1); }
+        s0 = fma(Pxx[i * 9 + 8], A[24 + j], s0);
+        hd->MA[it] = s0 + s1;
+      } else if (it < 45) {
+        const int e = it - 27, m = e / 9, j = e - 9 * m;
+        hd->G[e] = m == 0 ? fma(B[0], Pxx[j], fma(B[1], Pxx[9 + j], fma(B[2], Pxx[18 + j], Pvx[j])))
+                          : fma(B[3], Pxx[j], Pvx[9 + j]);
+      } else if (it < 54) {
+        const int i = it - 45;
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int l = 0; l < 8; l += 2) { s0 = fma(Pxx[i * 9 + l], d[l], s0); s1 = fma(Pxx[i * 9 + l + 1], d[l + 1], s1); }
+        hd->ev[i] = fma(Pxx[i * 9 + 8], d[8], s0) + s1;
+      } else if (it < 56) {
+        const int m = it - 54;
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int l = 0; l < 8; l += 2) { s0 = fma(Pvx[m * 9 + l], d[l], s0); s1 = fma(Pvx[m * 9 + l + 1], d[l + 1], s1); }
+        hd->fv[m] = fma(Pvx[m * 9 + 8], d[8], s0) + s1;
+      } else {
+        const int q = it - 56;  // Huu entries 00, 01, 11
+        const double* db = c.D + c.Rs + 4 * k;
+        // (Pxx+ b)_i for b = (B0, B1, B2, 0...) and the products with the two columns of B
+        const double pb0 = fma(Pxx[0], B[0], fma(Pxx[1], B[1], Pxx[2] * B[2]));
+        double v;
+        if (q == 0) {
+          const double pb1 = fma(Pxx[9], B[0], fma(Pxx[10], B[1], Pxx[11] * B[2]));
+          const double pb2 = fma(Pxx[18], B[0], fma(Pxx[19], B[1], Pxx[20] * B[2]));
+          const double bPb = fma(B[0], pb0, fma(B[1], pb1, B[2] * pb2));
+          const double pvb = fma(Pvx[0], B[0], fma(Pvx[1], B[1], Pvx[2] * B[2]));
+          v = hd->R2[0] + db[0] + db[1] + dR2[0] + bPb + 2.0 * pvb + Pvv[0];
+        } else if (q == 1) {
+          const double pvb10 = fma(Pvx[9], B[0], fma(Pvx[10], B[1], Pvx[11] * B[2]));  // (Pvx B)[1][0]
+          v = hd->R2[1] + dR2[1] + B[3] * pb0 + Pvx[0] * B[3] + pvb10 + Pvv[1];
+        } else {
+          v = hd->R2[3] + db[2] + db[3] + dR2[3] + B[3] * B[3] * Pxx[0] + 2.0 * Pvx[9] * B[3] + Pvv[3];
+        }
+        hd->Huu[q] = v;
+      }
+    }
+    Q3_SYNC();
+    // ---- phase 2
+    Q3_FOR(it, 24) {
+      if (it < 6) {  // TA upper triangle
+        const int i = it < 3 ? 0 : (it < 5 ? 1 : 2), j = it < 3 ? it : (it < 5 ? it - 2 : 2);
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int l = 0; l < 8; l += 2) { s0 = fma(A[l * 3 + i], hd->MA[l * 3 + j], s0); s1 = fma(A[(l + 1) * 3 + i], hd->MA[(l + 1) * 3 + j], s1); }
+        const double v = fma(A[24 + i], hd->MA[24 + j], s0) + s1;
+        hd->TA[i * 3 + j] = v; hd->TA[j * 3 + i] = v;
+      } else if (it < 12) {
+        const int e = it - 6, m = e / 3, j = e - 3 * m;
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int l = 0; l < 8; l += 2) { s0 = fma(hd->G[m * 9 + l], A[l * 3 + j], s0); s1 = fma(hd->G[m * 9 + l + 1], A[(l + 1) * 3 + j], s1); }
+        hd->Fs[e] = fma(hd->G[m * 9 + 8], A[24 + j], s0) + s1;
+      } else if (it < 21) {
+        const int j = it - 12;
+        double v;
+        if (j < 3) {
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int l = 0; l < 8; l += 2) { s0 = fma(A[l * 3 + j], px[l] + hd->ev[l], s0); s1 = fma(A[(l + 1) * 3 + j], px[l + 1] + hd->ev[l + 1], s1); }
+          v = fma(A[24 + j], px[8] + hd->ev[8], s0) + s1;
+        } else {
+          v = px[j] + hd->ev[j];
+        }
+        hd->Apx[j] = v;
+      } else if (it < 23) {
+        const int m = it - 21;
+        const double p0 = px[0] + hd->ev[0];
+        double v = c.gu[2 * k + m] + pv[m] + hd->fv[m];
+        if (m == 0) v += fma(B[0], p0, fma(B[1], px[1] + hd->ev[1], B[2] * (px[2] + hd->ev[2])));
+        else v = fma(B[3], p0, v);
+        hd->hu[m] = v;
+      } else {
+        const double h00 = hd->Huu[0], h01 = hd->Huu[1], h11 = hd->Huu[2];
+        const double idet = 1.0 / (h00 * h11 - h01 * h01);
+        double* W = c.Wi + 4 * k;
+        W[0] = h11 * idet; W[1] = -h01 * idet; W[2] = h00 * idet;
+      }
+    }
+    Q3_SYNC();
+    // ---- phase 3: the stage's outputs, then P_k
+    const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
+    const double z0 = W00 * hd->hu[0] + W01 * hd->hu[1], z1 = W01 * hd->hu[0] + W11 * hd->hu[1];
+    Q3_FOR(e, 18) {
+      const int m = e / 9, j = e - 9 * m;
+      c.F[18 * k + e] = j < 3 ? hd->Fs[m * 3 + j] : hd->G[e];
+    }
+    Q3_FOR(e, 2) c.zk[2 * k + e] = e == 0 ? z0 : z1;
+    if (k > 0) {
+      Q3_FOR(it, 45 + 18 + 3 + 9 + 2) {
+        if (it < 45) {
+          const int ij = hd->tri[it], i = ij >> 4, j = ij & 15;
+          const double f0i = i < 3 ? hd->Fs[i] : hd->G[i], f1i = i < 3 ? hd->Fs[3 + i] : hd->G[9 + i];
+          const double f0j = j < 3 ? hd->Fs[j] : hd->G[j], f1j = j < 3 ? hd->Fs[3 + j] : hd->G[9 + j];
+          const double T = j < 3 ? hd->TA[i * 3 + j] : (i < 3 ? hd->MA[j * 3 + i] : Pxx[i * 9 + j]);
+          const double v = T - (W00 * (f0i * f0j) + W01 * (f0i * f1j + f1i * f0j) + W11 * (f1i * f1j)) + qt3(c, k - 1, i, j);
+          Pxx[i * 9 + j] = v; Pxx[j * 9 + i] = v;
+        } else if (it < 63) {
+          const int e = it - 45, m = e / 9, j = e - 9 * m;
+          const double f0j = j < 3 ? hd->Fs[j] : hd->G[j], f1j = j < 3 ? hd->Fs[3 + j] : hd->G[9 + j];
+          const double fw0 = W00 * f0j + W01 * f1j, fw1 = W01 * f0j + W11 * f1j;
+          Pvx[e] = dR2[m * 2] * fw0 + dR2[m * 2 + 1] * fw1;
+        } else if (it < 66) {
+          const int q = it - 63, m = q == 2 ? 1 : 0, n = q == 0 ? 0 : 1;
+          // (dR2 W dR2)[m][n]
+          const double a0 = dR2[m * 2] * W00 + dR2[m * 2 + 1] * W01, a1 = dR2[m * 2] * W01 + dR2[m * 2 + 1] * W11;
+          const double v = dR2[m * 2 + n] - (a0 * dR2[n] + a1 * dR2[2 + n]);
+          Pvv[m * 2 + n] = v; Pvv[n * 2 + m] = v;
+        } else if (it < 75) {
+          const int j = it - 66;
+          const double f0j = j < 3 ? hd->Fs[j] : hd->G[j], f1j = j < 3 ? hd->Fs[3 + j] : hd->G[9 + j];
+          px[j] = hd->Apx[j] - f0j * z0 - f1j * z1 + c.gx[9 * (k - 1) + j];
+        } else {
+          const int m = it - 75;
+          pv[m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1;
+        }
+      }
+    }
+    Q3_SYNC();
+  }
+}
+
+// Backward pass for a new gradient with the factor kept from ric_factor_backward3 (zero defects).
+// ye != nullptr: the costates are written as the multipliers of the dynamics rows (rows of G, LPV_Planner.py:429-475):
+// ye[12 t + j] = -px_t[j], t = N .. 1, and row block 0 from one adjoint step (gq0 = gradient of the cost in x_0).
+Q3D void ric_affine_backward3(const Ctx3& c, double* ye) {
+  Hdr3* hd = c.hd;
+  const int N = c.N;
+  const double* dR2 = hd->dR2;
+  Q3_FOR(e, 9) hd->px[0][e] = c.gx[9 * (N - 1) + e];
+  Q3_FOR(e, 2) hd->pv[0][e] = 0.0;
+  Q3_SYNC();
+  int cur = 0;
+#pragma unroll 1
+  for (int k = N - 1; k >= 0; --k) {
+    const double* A = c.Acol + 27 * k;
+    const double* B = c.Bcol + 4 * k;
+    const double* pin = hd->px[cur];
+    const double* pvin = hd->pv[cur];
+    const double* Fk = c.F + 18 * k;
+    const double hu0 = c.gu[2 * k] + pvin[0] + fma(B[0], pin[0], fma(B[1], pin[1], B[2] * pin[2]));
+    const double hu1 = c.gu[2 * k + 1] + pvin[1] + B[3] * pin[0];
+    const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
+    const double z0 = W00 * hu0 + W01 * hu1, z1 = W01 * hu0 + W11 * hu1;
+    Q3_FOR(it, 13) {
+      if (it < 9) {
+        const int j = it;
+        double v;
+        if (j < 3) {
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int l = 0; l < 8; l += 2) { s0 = fma(A[l * 3 + j], pin[l], s0); s1 = fma(A[(l + 1) * 3 + j], pin[l + 1], s1); }
+          v = fma(A[24 + j], pin[8], s0) + s1;
+        } else {
+          v = pin[j];
+        }
+        if (ye) ye[12 * (k + 1) + j] = -pin[j];
+        if (k > 0) hd->px[cur ^ 1][j] = v - Fk[j] * z0 - Fk[9 + j] * z1 + c.gx[9 * (k - 1) + j];
+        else if (ye) {
+          double gq = j == 0 ? hd->q0 : 0.0;
+          for (int l = 0; l < 9; ++l) gq = fma(hd->Q2[j * 9 + l], hd->x0[l], gq);
+          ye[j] = -(v + gq);
+        }
+      } else if (it < 11) {
+        const int m = it - 9;
+        hd->pv[cur ^ 1][m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1;
+      } else {
+        c.zk[2 * k + (it - 11)] = it == 11 ? z0 : z1;
+      }
+    }
+    Q3_SYNC();
+    cur ^= 1;
+  }
+}
+
+// Forward pass: c.du, c.dx (c.dx holds the defects on input), then the slack steps from c.gs.  acc: the sweep's step is
+// ADDED to c.dx / c.du (corrector increment on top of the predictor; no defects) - the slack steps, linear in (dx, gs),
+// are recomputed from the totals.  Ends with a barrier.
+Q3D void ric_forward3(const Ctx3& c, int acc) {
+  Hdr3* hd = c.hd;
+  const double* dR2 = hd->dR2;
+  int cur = 0;
+#pragma unroll 1
+  for (int k = 0; k < c.N; ++k) {
+    const double* A = c.Acol + 27 * k;
+    const double* B = c.Bcol + 4 * k;
+    const double* Fk = c.F + 18 * k;
+    const double* xin = hd->fx[cur];
+    const double* vin = hd->fu[cur];
+    double du0 = -c.zk[2 * k], du1 = -c.zk[2 * k + 1];
+    if (k > 0) {
+      double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+#pragma unroll
+      for (int l = 0; l < 8; l += 2) {
+        t0 = fma(Fk[l], xin[l], t0); t1 = fma(Fk[l + 1], xin[l + 1], t1);
+        t2 = fma(Fk[9 + l], xin[l], t2); t3 = fma(Fk[9 + l + 1], xin[l + 1], t3);
+      }
+      const double r0 = fma(Fk[8], xin[8], t0) + t1 - (dR2[0] * vin[0] + dR2[1] * vin[1]);
+      const double r1 = fma(Fk[17], xin[8], t2) + t3 - (dR2[2] * vin[0] + dR2[3] * vin[1]);
+      const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
+      du0 -= W00 * r0 + W01 * r1;
+      du1 -= W01 * r0 + W11 * r1;
+    }
+    Q3_FOR(it, 11) {
+      if (it < 9) {
+        double v = (k > 0 ? arow3(A, xin, it) : 0.0) + brow3(B, du0, du1, it);
+        if (!acc) v += c.dx[9 * k + it];
+        hd->fx[cur ^ 1][it] = v;
+        c.dx[9 * k + it] = acc ? c.dx[9 * k + it] + v : v;
+      } else {
+        const double v = it == 9 ? du0 : du1;
+        hd->fu[cur ^ 1][it - 9] = v;
+        c.du[2 * k + (it - 9)] = acc ? c.du[2 * k + (it - 9)] + v : v;
+      }
+    }
+    Q3_SYNC();
+    cur ^= 1;
+  }
+  // slack steps: dsig = -Si (bh' do + gs)
+  Q3_FOR(t, c.N) {
+    const double* si = c.Si + 6 * t;
+    const double* bh = c.bh + 4 * t;
+    const double* d = c.dx + 9 * t;
+    const double r0 = -(c.gs[3 * t + 0] + bh[0] * d[0]);
+    const double r1 = -(c.gs[3 * t + 1] + bh[1] * d[3]);
+    const double r2 = -(c.gs[3 * t + 2] + bh[2] * d[7] + bh[3] * d[8]);
+    c.dsig[3 * t + 0] = si[0] * r0 + si[1] * r1 + si[2] * r2;
+    c.dsig[3 * t + 1] = si[1] * r0 + si[3] * r1 + si[4] * r2;
+    c.dsig[3 * t + 2] = si[2] * r0 + si[4] * r1 + si[5] * r2;
+  }
+  Q3_SYNC();
+}
+
+// One instantiation each of the two solves (they are called from the active-set rounds and from the interior point).
+// c.D must be final and barrier-visible.  mode / smu: see assemble_gradient3.
+Q3N void factor_solve3(int mode) {
+  Q3_CTX(c);
+  stage_weights3(c);
+  assemble_gradient3(c, mode, 0.0, 1);
+  ric_factor_backward3(c);
+  ric_forward3(c, 0);
+  if (Q3_LANE == 0) { ++c.hd->n_fact; ++c.hd->n_solve; }
+}
+Q3N void affine_solve3(int mode, double smu) {
+  Q3_CTX(c);
+  assemble_gradient3(c, mode, smu, 0);
+  ric_affine_backward3(c, nullptr);
+  ric_forward3(c, mode == G3_COR);
+  if (Q3_LANE == 0) ++c.hd->n_solve;
+}
+
+// z <- z + alpha dz for the primal variables; returns max |dz| / (1 + max |z|) (all lanes).  Ends with a barrier.
+Q3D double primal_step3(const Ctx3& c, double alpha) {
+  double vm = 0.0, zm = 0.0;
+  Q3_FOR(j, 9 * c.N) { zm = fmax(zm, fabs(c.x[j])); vm = fmax(vm, fabs(c.dx[j])); c.x[j] = fma(alpha, c.dx[j], c.x[j]); }
+  Q3_FOR(j, 2 * c.N) { zm = fmax(zm, fabs(c.u[j])); vm = fmax(vm, fabs(c.du[j])); c.u[j] = fma(alpha, c.du[j], c.u[j]); }
+  Q3_FOR(j, 3 * c.N) { c.sig[j] = fma(alpha, c.dsig[j], c.sig[j]); }
+  vm = q3_wmax(vm); zm = q3_wmax(zm);
+  Q3_SYNC();
+  return alpha * vm / (1.0 + zm);
+}

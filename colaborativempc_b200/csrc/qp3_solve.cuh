@@ -1,0 +1,286 @@
+// qp3_solve.cuh - exact QP solve on the stage-wise engine (qp3_engine.cuh).
+//
+// Replaces the OSQP call of distributedPlanner/LPV_Planner.py:222-249 (setup + solve + polish).  The returned point is
+// the KKT-certified optimum of the reference's QP (what OSQP converges to as eps -> 0):
+//   1. primal-dual active-set rounds: the rows of the guess get the penalty 1/delta (OSQP's polish, LPV_Planner.py:233
+//      polish=True, restated stage-wise), the multipliers are refined by the method of multipliers, the guess is updated
+//      from the signs (violated rows in, negative multipliers out) until the KKT certificate holds;
+//   2. a Mehrotra predictor-corrector interior-point phase when the rounds cycle or run out, whose complementarity
+//      pattern seeds the next rounds; the phase continues from its own iterate at a tighter target if they fail.
+// Every linear solve is a Riccati sweep; nothing here depends on the horizon except loop lengths.
+#pragma once
+#include "qp3_engine.cuh"
+
+// loose thresholds that decide "the guess is clearly wrong, do not spend refinement passes on it"
+#define Q3_LOOSE 1e-6
+
+// One active-set round on c.act.  Returns 1 certified, 0 guess updated (c.act), 2 numerical failure (non-finite).
+// On exit c.x, c.u, c.sig, c.lam, c.res belong to the guess that was solved.
+Q3N int polish_round3() {
+  Q3_CTX(c);
+  Hdr3* hd = c.hd;
+  // Penalty of the rows in the guess.  A soft row (one with a slack) is only ever as stiff as its slack weight: after
+  // the slack elimination its weight is D 2Qs / (2Qs + D) -> 2Qs, so the multiplier iteration contracts by 2Qs / D per
+  // pass on it; it gets 1e3 / delta (hard rows: curvature of the cost, a few 1e2, over 1 / delta).
+#ifndef Q3_SOFT
+#define Q3_SOFT 10.0
+#endif
+  const double Dv = 1.0 / hd->delta, Ds = Q3_SOFT * Dv, cert_tol = hd->cert_tol;
+  Q3_FOR(j, c.RT) {
+    const bool soft = j < c.Rs && (c.rinfo[j] & 127) != 0;
+    c.D[j] = (c.act[j] && row_ok3(c, j)) ? (soft ? Ds : Dv) : 0.0;
+    c.lam[j] = 0.0;
+  }
+  Q3_SYNC();
+  eval_residuals3(c);
+  factor_solve3(G3_ALM);
+  primal_step3(c, 1.0);
+  int pass = 0;
+#pragma unroll 1
+  for (;;) {
+    eval_residuals3(c);
+    // multiplier update, then: how far are the active rows from their bounds, is the guess still plausible
+    double v = 0.0, lm = 0.0, dl = 0.0;
+    int bad = 0;
+    Q3_FOR(j, c.RT) {
+      const double l = fma(c.D[j], c.res[j], c.lam[j]);
+      dl = fmax(dl, fabs(c.D[j] * c.res[j]));
+      c.lam[j] = l;
+      if (!(fabs(c.res[j]) < 1e300) || !(fabs(l) < 1e300)) bad = 1;
+      lm = fmax(lm, fabs(l));
+      if (c.D[j] > 0.0) v = fmax(v, fabs(c.res[j]) / (1.0 + fabs(row_b3(c, j))));
+    }
+    if (q3_wor(bad)) return 2;
+    lm = 1.0 + q3_wmax(lm);
+    v = q3_wmax(v);
+    dl = q3_wmax(dl);
+    Q3_SYNC();
+#ifdef QP3_TRACE
+    { double dl = 0; for (int j = 0; j < c.RT; ++j) dl = fmax(dl, fabs(c.D[j] * c.res[j])); int na = 0; for (int j = 0; j < c.RT; ++j) na += c.act[j];
+      printf("  pass %d v %.3e dlam %.3e lm %.3e nact %d\n", pass, v, dl, lm, na); }
+#endif
+    // converged: active rows on their bounds AND the multiplier iteration has stopped moving (the last update is what
+    // the multipliers are still off by, times the contraction of a pass)
+    const bool tight = pass >= 1 && v <= 0.1 * cert_tol && (dl <= 1e-7 * lm || pass >= hd->refine);
+    const double tol = tight ? cert_tol : Q3_LOOSE;
+    int changed = 0;
+    Q3_FOR(j, c.RT) {
+      if (!row_ok3(c, j)) continue;
+      if (!c.act[j]) { if (c.res[j] > tol * (1.0 + fabs(row_b3(c, j)))) changed = 1; }
+      else if (c.lam[j] < -tol * lm) changed = 1;
+    }
+    changed = q3_wor(changed);
+    if (tight && !changed) return 1;
+    if (changed || pass >= hd->refine) {
+      // update the guess with the tight thresholds (a row the loose test let through still moves)
+      Q3_FOR(j, c.RT) {
+        if (!row_ok3(c, j)) continue;
+        if (!c.act[j]) { if (c.res[j] > cert_tol * (1.0 + fabs(row_b3(c, j)))) c.act[j] = 1; }
+        else if (c.lam[j] < -cert_tol * lm) c.act[j] = 0;
+      }
+      Q3_SYNC();
+      return 0;
+    }
+    affine_solve3(G3_ALM, 0.0);
+    primal_step3(c, 1.0);
+    ++pass;
+  }
+}
+
+// order-independent 64-bit hash of the active set
+Q3D unsigned long long act_hash3(const Ctx3& c) {
+  unsigned long long h = 0;
+  Q3_FOR(j, c.RT)
+    if (c.act[j]) {
+      unsigned long long x = (unsigned long long)(j + 1) * 0x9E3779B97F4A7C15ull;
+      x ^= x >> 29; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 32;
+      h += x;
+    }
+  return q3_wsum64(h);
+}
+
+// Up to `rounds` rounds; 1 certified, 0 not (cycle or round cap), 2 numerical failure.
+Q3N int pdas3(int rounds) {
+  Q3_CTX(c);
+  int nh = 0;
+#pragma unroll 1
+  for (int r = 0; r < rounds; ++r) {
+    const int st = polish_round3();
+    if (Q3_LANE == 0) ++c.hd->n_rounds;
+    if (st) return st;
+    const unsigned long long h = act_hash3(c);
+    int cyc = 0;
+    for (int i = 0; i < nh && i < 16; ++i) cyc |= (c.hd->hist[i] == h);
+    Q3_SYNC();
+    if (Q3_LANE == 0 && nh < 16) c.hd->hist[nh] = h;
+    ++nh;
+    Q3_SYNC();
+    if (cyc) return 0;
+  }
+  return 0;
+}
+
+// largest alpha in (0, 1] with x + alpha dx >= 0 over the valid rows
+Q3D double step_to_boundary3(const Ctx3& c, const double* x, const double* dx) {
+  double a = 1.0;
+  Q3_FOR(j, c.RT)
+    if (row_ok3(c, j) && dx[j] < 0.0) a = fmin(a, -x[j] / dx[j]);
+  return q3_wmin(a);
+}
+
+// interior-point iterate (x, u, sigma, lambda, t) <-> the QP's global scratch slice.  Ends with a barrier.
+Q3D void ipm_park3(const Ctx3& c, double* park, int save) {
+  double* const v[5] = {c.x, c.u, c.sig, c.lam, c.tt};
+  const int len[5] = {9 * c.N, 2 * c.N, 3 * c.N, c.RT, c.RT};
+  double* p = park;
+  for (int q = 0; q < 5; ++q) {
+    Q3_FOR(j, len[q]) {
+      if (save) p[j] = v[q][j];
+      else v[q][j] = p[j];
+    }
+    p += len[q];
+  }
+  Q3_SYNC();
+}
+
+// Mehrotra predictor-corrector down to complementarity mu_tol.  warm: continue from the parked iterate.
+// One step length for primal and dual (the Hessian couples them): every linear residual - dual, primal, dynamics -
+// then contracts by exactly (1 - alpha) per iteration, which is how the dual residual is tracked (its costates are
+// implicit in the Riccati sweep).  Returns 0 converged, 1 diverged, 2 iteration cap, 3 non-finite.
+Q3N int ipm3(double mu_tol, int warm, double* park) {
+  Q3_CTX(c);
+  Hdr3* hd = c.hd;
+  const int ipm_max = hd->ipm_max;
+  const int m = c.N * (4 + c.cnt) + 4 * c.N;
+  double lin = 1.0;  // product of (1 - alpha): scale of the linear residuals relative to the phase's start
+  if (warm) {
+    ipm_park3(c, park, 0);
+  } else {
+    // ---- starting point: least squares with unit row weights from a bounded point, then shift into the cone
+    Q3_FOR(j, c.RT) { c.D[j] = row_ok3(c, j) ? 1.0 : 0.0; c.lam[j] = 0.0; }
+    Q3_FOR(j, 9 * c.N) c.x[j] = hd->x0[j % 9];
+    Q3_FOR(j, 2 * c.N) c.u[j] = 0.0;
+    Q3_FOR(j, 3 * c.N) c.sig[j] = 0.0;
+    Q3_SYNC();
+    eval_residuals3(c);
+    factor_solve3(G3_ALM);
+    primal_step3(c, 1.0);
+    eval_residuals3(c);
+    const double qsm = 0.5 * fmax(hd->Qs2[0], fmax(hd->Qs2[4], hd->Qs2[8]));
+    const double lam_scale = fmax(1.0, 1e-3 * qsm);
+    double mt = 1e300, ml = 1e300;
+    Q3_FOR(j, c.RT)
+      if (row_ok3(c, j)) { mt = fmin(mt, -c.res[j]); ml = fmin(ml, c.res[j]); }
+    mt = q3_wmin(mt); ml = q3_wmin(ml);
+    Q3_FOR(j, c.RT) {
+      if (!row_ok3(c, j)) { c.tt[j] = 1.0; c.lam[j] = 0.0; continue; }
+      double t = -c.res[j], l = c.res[j];
+      if (mt < 0.0) t += 1.0 - mt;
+      if (ml < 0.0) l += 1.0 - ml;
+      c.tt[j] = fmax(t, 1e-8); c.lam[j] = lam_scale * fmax(l, 1e-8);
+    }
+    Q3_SYNC();
+  }
+  // scale of the dual residual at the start: the least-squares point is stationary for lam = res, so what is left is
+  // C'(lam - res); bounded by the multiplier scale (a warm start continues a converged phase: same bound)
+  double v_l = 0.0;
+  Q3_FOR(j, c.RT) if (row_ok3(c, j)) v_l = fmax(v_l, c.lam[j]);
+  const double rd0 = (double)(4 + c.cnt) * (1.0 + q3_wmax(v_l));
+  double gmax = 1.0 + fabs(hd->q0);
+#pragma unroll 1
+  for (int it = 0; it < ipm_max; ++it) {
+    eval_residuals3(c);
+    double v_mu = 0.0, v_rp = 0.0, v_lm = 0.0;
+    Q3_FOR(j, c.RT)
+      if (row_ok3(c, j)) { v_mu = fma(c.lam[j], c.tt[j], v_mu); v_rp = fmax(v_rp, fabs(c.res[j] + c.tt[j])); v_lm = fmax(v_lm, c.lam[j]); }
+    double v_obj = 0.0;
+    Q3_FOR(k, c.N) {  // scale of the objective (the exact value is computed by the epilogue)
+      const double* xk = c.x + 9 * k;
+      for (int i = 0; i < 9; ++i) v_obj += xk[i] * (0.5 * hd->Q2[i * 9 + i] * xk[i]);
+      v_obj += hd->q0 * xk[0];
+    }
+    const double mu = q3_wsum(v_mu) / m;
+    const double rp = q3_wmax(v_rp), lmax = q3_wmax(v_lm);
+    const double obj = fabs(q3_wsum(v_obj));
+    const double rd = lin * rd0;
+    if (Q3_LANE == 0) ++hd->n_ipm;
+    if (!isfinite(mu) || !isfinite(rp)) return 3;
+    if (!(mu < 1e40) || !(rp < 1e40)) return 1;
+    if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * (gmax + lmax)) return 0;
+    // ---- predictor (factorisation for D = lam / t)
+    Q3_FOR(j, c.RT) c.D[j] = row_ok3(c, j) ? c.lam[j] / c.tt[j] : 0.0;
+    Q3_SYNC();
+    factor_solve3(G3_AFF);
+    Q3_FOR(j, c.RT) {
+      if (!row_ok3(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
+      const double dt = -(c.res[j] + c.tt[j]) - row_val3(c, j, c.dx, c.dsig, c.du);
+      c.dtt[j] = dt;
+      c.dlam[j] = -(c.lam[j] + c.D[j] * dt);
+    }
+    Q3_SYNC();
+    const double aa = fmin(step_to_boundary3(c, c.tt, c.dtt), step_to_boundary3(c, c.lam, c.dlam));
+    double v_aff = 0.0;
+    Q3_FOR(j, c.RT)
+      if (row_ok3(c, j)) v_aff = fma(c.lam[j] + aa * c.dlam[j], c.tt[j] + aa * c.dtt[j], v_aff);
+    const double mu_aff = q3_wsum(v_aff) / m;
+    const double sr = mu_aff / mu, smu = sr * sr * sr * mu;
+    // ---- corrector increment: same factor, right-hand side (smu - dt_aff dlam_aff) / t on the rows only; by linearity
+    // its step is added to the predictor's in place (dx, du, and the slack steps from the summed slack gradient)
+    affine_solve3(G3_COR, smu);
+    Q3_FOR(j, c.RT) {
+      if (!row_ok3(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
+      const double dt = -(c.res[j] + c.tt[j]) - row_val3(c, j, c.dx, c.dsig, c.du);
+      const double rc = c.lam[j] * c.tt[j] + c.dtt[j] * c.dlam[j] - smu;
+      c.dtt[j] = dt;
+      c.dlam[j] = -(rc + c.lam[j] * dt) / c.tt[j];
+    }
+    Q3_SYNC();
+    const double al = fmin(1.0, 0.99 * fmin(step_to_boundary3(c, c.tt, c.dtt), step_to_boundary3(c, c.lam, c.dlam)));
+    primal_step3(c, al);
+    Q3_FOR(j, c.RT) {
+      c.tt[j] = fma(al, c.dtt[j], c.tt[j]);
+      c.lam[j] = fma(al, c.dlam[j], c.lam[j]);
+    }
+    Q3_SYNC();
+    lin *= 1.0 - al;
+  }
+  return 2;
+}
+
+// Full solve.  Returns dmpc_status; the header counts the work done.  `park`: the QP's global scratch slice.
+Q3D int solve_qp3(const Ctx3& c, double* park) {
+  Hdr3* hd = c.hd;
+  // first guess: the empty working set, from a bounded (not dynamics-consistent) point; the first solve removes the
+  // dynamics defects, so the round returns the unconstrained optimum and adds the rows it violates
+  Q3_FOR(j, c.RT) c.act[j] = 0;
+  Q3_FOR(j, 9 * c.N) c.x[j] = hd->x0[j % 9];
+  Q3_FOR(j, 2 * c.N) c.u[j] = 0.0;
+  Q3_FOR(j, 3 * c.N) c.sig[j] = 0.0;
+  Q3_SYNC();
+  {
+    const int st = pdas3(3 * hd->pdas_first);  // same budget as the condensed engine's free rounds
+    if (st == 1) return DMPC_SOLVED;
+  }
+  double mu_tol = hd->ipm_mu0, mu_ok = 0.0;
+#pragma unroll 1
+  while (mu_tol > 1e-13) {
+    const int rc = ipm3(mu_tol, mu_ok > 0.0, park);
+    if (rc == 1 || rc == 3) {  // divergence of the FIRST phase = infeasible hard rows; later phases only lose accuracy
+      if (mu_ok == 0.0) return rc == 3 ? DMPC_UNSOLVED : DMPC_PRIMAL_INFEASIBLE;
+      break;
+    }
+    if (rc == 0) { mu_ok = mu_tol; ipm_park3(c, park, 1); }
+    Q3_FOR(j, c.RT) c.act[j] = row_ok3(c, j) && (c.lam[j] > c.tt[j]);
+    Q3_SYNC();
+    if (pdas3(hd->pdas_after) == 1) return DMPC_SOLVED;
+    if (rc == 2) break;  // iteration cap: a tighter target from the same start would hit it again
+    mu_tol *= 1e-2;
+  }
+  if (mu_ok > 0.0) {  // no active set certified (degenerate rows): hand back the tightest interior-point iterate
+    ipm_park3(c, park, 0);
+    Q3_FOR(j, c.RT) if (!row_ok3(c, j)) c.lam[j] = 0.0;
+    Q3_SYNC();
+    return DMPC_SOLVED_INACCURATE;
+  }
+  return DMPC_MAX_ITER_REACHED;
+}

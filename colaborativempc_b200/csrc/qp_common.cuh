@@ -6,52 +6,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#include "../../include/dmpc_b200.h"
+#include "qp_types.h"
 
 #define QP_THREADS 128
 #define QP_WARPS (QP_THREADS / 32)
-#define NSTATE 9
-
-struct DevParams {
-  int N, nn, nseg, nrows;   // nrows: state rows of the prediction matrices kept on chip
-  int rowsel[NSTATE];       // state index of each kept row; the first four are always vx(0), e_y(3), x(7), y(8)
-  int nq;                   // nonzeros of the upper triangle of Q
-  int qa[45], qb[45];       // positions (in rowsel order) of Q's nonzeros
-  double qv[45];
-  double dt, wq, Q00;
-  double Qs[9], R[4], dR[4];
-  double lf, lr, m, I, Cf, Cr, mu;
-  double vx_ref, min_dist, max_vel, min_vel, max_rs, max_ls, max_ac, max_dc;
-  double seg_s0[DMPC_MAX_SEG], seg_len[DMPC_MAX_SEG], seg_curv[DMPC_MAX_SEG], seg_hw[DMPC_MAX_SEG];
-  // solver options
-  double delta;             // polish regularisation (multiplier-refinement penalty 1/delta)
-  double cert_tol;          // relative KKT certificate tolerance
-  double ipm_mu0;           // first interior-point complementarity target
-  int refine;               // multiplier refinement steps per polish round
-  int pdas_first;           // active-set rounds tried before the interior-point phase
-  int pdas_after;           // active-set rounds after each interior-point phase
-  int ipm_max;              // interior-point iteration cap per phase
-  int gr_global, hk_global; // 1: prediction rows / Hessian+factor live in the global workspace (long horizons)
-};
-
-struct BatchPtrs {
-  int B, xprev_rows;
-  const double *x0, *xprev, *uprev, *uold, *nbr_xy, *pose;
-  const int* nbr_count;
-  double *z, *planes, *y_ineq, *y_eq, *obj;
-  int *status, *iters, *pivots;
-  double* gws;              // global workspace, gws_stride doubles per QP
-  long long gws_stride;
-  // launch order of the fast engine: CTA i solves QP order[i] (nullptr = identity) and records what the solve cost in
-  // cost[]; order_by_cost_kernel turns that into the next call's order, most expensive first, so the few QPs that
-  // need the interior-point phase do not start at the end of the grid and become the tail of the launch
-  const int* order;
-  int* cost;
-  // split launch: order[0 .. *nhard) are the QPs that needed the interior-point phase last time; part 1 (side stream,
-  // one CTA per SM) solves exactly those, part 2 (main launch) skips them; part 0: one launch does everything
-  const int* nhard;
-  int part;
-};
 
 // ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ double warp_max(double v) {
@@ -105,10 +63,17 @@ __device__ __forceinline__ int block_or(int v, int* redi) {
 
 // Track lookup with the semantics of utilities/misc.py:78-101 / :105-126: wrap while s > L, clamp s < 0,
 // segment i with s0[i] <= s < s0[i]+len[i]; -1 where the reference's int(np.where(...)) raises.
+// The wrap is one floor-based reduction plus a fix-up that keeps the reference's s == k L behaviour (its loop stops at
+// the first value <= L, so an exact multiple of L ends at L, where no segment matches); |s| beyond 1e6 track lengths
+// is reported as a failed lookup instead of being walked down.
 __device__ __forceinline__ int map_segment(const DevParams& P, double s) {
   const double L = P.seg_s0[P.nseg - 1] + P.seg_len[P.nseg - 1];
-  if (!(s == s) || !(L > 0.0) || fabs(s) > 1e12) return -1;
-  while (s > L) s -= L;
+  if (!(s == s) || !(L > 0.0) || fabs(s) > 1e6 * L) return -1;
+  if (s > L) {
+    s -= L * floor(s / L);
+    if (s <= 0.0) s += L;
+    while (s > L) s -= L;
+  }
   if (s < 0.0) s = 0.0;
   int found = -1, cnt = 0;
   for (int i = 0; i < P.nseg; ++i)

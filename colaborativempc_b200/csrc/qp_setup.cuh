@@ -3,9 +3,9 @@
 // Reference functions replaced (paths relative to planner/lib/plan_lib/):
 //   planes/compute_plane.py:41-68 (compute_hyperplane, keep_sign=True), utilities/misc.py:10-26 (compute_weights),
 //   distributedPlanner/LPV_Planner.py:477-591 (_EstimateABC), utilities/misc.py:78-126 (curvature, get_ey),
-//   LPV_Planner.py:382-427 (_buildMatCost) and :429-475 (_buildMatEqConst, eliminated here by condensation).
+//   (the condensed engine's prediction rows and cost, LPV_Planner.py:382-475, are in qp2_kernel.cuh).
 #pragma once
-#include "qp_engine.cuh"
+#include "qp_common.cuh"
 
 // planes (N,3,nn) + distance weights folded into the linear cost of x,y (LPV_Planner.py:416-422).
 // Returns nonzero if ego and a neighbour coincide (compute_plane.py:52 divides by zero there).
@@ -108,86 +108,4 @@ __device__ __forceinline__ void lpv_step(const double* A, double* v) {  // v <- 
     s = fma(A[r * 3 + 0], v0, s); s = fma(A[r * 3 + 1], v1, s); s = fma(A[r * 3 + 2], v2, s);
     v[r] = s;
   }
-}
-
-// Prediction rows: x_t = cr_t + sum_j Gr_t[:, j] u_j for the kept state rows (one thread per input column,
-// plus one thread for the free response from x0).
-__device__ __forceinline__ void setup_prediction(const Ctx& c, const DevParams& P, const double* x0) {
-  for (int j = threadIdx.x; j <= c.nu; j += QP_THREADS) {
-    double v[9];
-    if (j == c.nu) {
-#pragma unroll
-      for (int r = 0; r < 9; ++r) v[r] = x0[r];
-      for (int t = 0; t < c.N; ++t) {
-        lpv_step(c.Acol + 27 * t, v);
-        for (int r = 0; r < c.NR; ++r) c.cr[t * c.NR + r] = v[P.rowsel[r]];
-      }
-    } else {
-      const int k = j >> 1;
-      for (int t = 0; t < k; ++t)
-        for (int r = 0; r < c.NR; ++r) GR(c, t, r, j) = 0.0;
-#pragma unroll
-      for (int r = 0; r < 9; ++r) v[r] = 0.0;
-      const double* B = c.Bcol + 4 * k;
-      if (j & 1) v[0] = B[3]; else { v[0] = B[0]; v[1] = B[1]; v[2] = B[2]; }
-      for (int t = k; t < c.N; ++t) {
-        if (t > k) lpv_step(c.Acol + 27 * t, v);
-        for (int r = 0; r < c.NR; ++r) GR(c, t, r, j) = v[P.rowsel[r]];
-      }
-    }
-  }
-}
-
-// H = 2 (Gamma' Qbar Gamma + Rbar + D' dRbar D),  g = 2 Gamma' (Qbar c + p) - 2 D' dRbar d0   (condensed cost).
-// `ql` is an N x NR scratch (uses c.Zb).
-__device__ __forceinline__ void setup_cost(const Ctx& c, const DevParams& P, const double* uold) {
-  double* ql = c.Zb;
-  for (int t = threadIdx.x; t < c.N; t += QP_THREADS) {
-    double* q = ql + t * c.NR;
-    for (int r = 0; r < c.NR; ++r) q[r] = 0.0;
-    const double* ct = c.cr + t * c.NR;
-    for (int e = 0; e < P.nq; ++e) {
-      const int a = P.qa[e], b = P.qb[e];
-      q[a] = fma(P.qv[e], ct[b], q[a]);
-      if (a != b) q[b] = fma(P.qv[e], ct[a], q[b]);
-    }
-    q[0] += -P.vx_ref * P.Q00;      // LPV_Planner.py:412
-    q[2] += c.pxy[2 * t];           // :421
-    q[3] += c.pxy[2 * t + 1];       // :422
-  }
-  __syncthreads();
-  for (int j = threadIdx.x; j < c.nu; j += QP_THREADS) {
-    double s = 0.0;
-    for (int t = j >> 1; t < c.N; ++t)
-      for (int r = 0; r < c.NR; ++r) s = fma(GR(c, t, r, j), ql[t * c.NR + r], s);
-    s *= 2.0;
-    if (j < 2) s -= 2.0 * (P.dR[j * 2 + 0] * uold[0] + P.dR[j * 2 + 1] * uold[1]);
-    c.g[j] = s;
-  }
-  const int ntri = c.nu * (c.nu + 1) / 2;
-  for (int e = threadIdx.x; e < ntri; e += QP_THREADS) {
-    int i = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
-    while ((i + 1) * (i + 2) / 2 <= e) ++i;
-    while (i * (i + 1) / 2 > e) --i;
-    const int j = e - i * (i + 1) / 2;
-    double s = 0.0;
-    for (int t = i >> 1; t < c.N; ++t)
-      for (int q = 0; q < P.nq; ++q) {
-        const int a = P.qa[q], b = P.qb[q];
-        double term = GR(c, t, a, i) * GR(c, t, b, j);
-        if (a != b) term = fma(GR(c, t, b, i), GR(c, t, a, j), term);
-        s = fma(P.qv[q], term, s);
-      }
-    s *= 2.0;
-    const int ki = i >> 1, kj = j >> 1, ai = i & 1, aj = j & 1;
-    if (ki == kj) {
-      s += 2.0 * (P.R[ai * 2 + aj] + P.dR[ai * 2 + aj]);
-      if (ki < c.N - 1) s += 2.0 * P.dR[ai * 2 + aj];
-    } else if (ki == kj + 1) {
-      s -= 2.0 * P.dR[ai * 2 + aj];
-    }
-    c.H[j * c.ldk + i] = s;
-    c.H[i * c.ldk + j] = s;
-  }
-  __syncthreads();
 }

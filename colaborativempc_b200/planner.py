@@ -14,7 +14,7 @@ import warnings
 import numpy as np
 
 from . import _abi
-from ._abi import DmpcBatchIO, DmpcOptions, make_params
+from ._abi import DmpcBatchIO, DmpcOptions, DmpcShiftIO, make_params
 
 FEASIBLE_STATUS = (_abi.SOLVED, _abi.SOLVED_INACCURATE, _abi.MAX_ITER_REACHED)  # LPV_Planner.py:246-248
 
@@ -53,7 +53,8 @@ class BatchedPlannerLPV(object):
             self.lib.dmpc_destroy(self._h)
             self._h = None
             raise DmpcError("dmpc_create failed (%d): %s" % (rc, msg))
-        self.fast = self.lib.dmpc_engine(self._h) == 2  # packed shared-memory engine (qp2_*.cuh) vs generic
+        self.engine = self.lib.dmpc_engine(self._h)      # _abi.ENGINE_STAGE (qp3_*.cuh) or _abi.ENGINE_FAST (qp2_*.cuh)
+        self.fast = self.engine == _abi.ENGINE_FAST
         self.n = 16 * self.N + 12
         self.m_in = (8 + self.nn) * self.N
         self.m_eq = 14 * self.N + 12
@@ -106,8 +107,11 @@ class BatchedPlannerLPV(object):
             setattr(io, k, ptr(outs.get(k)))
         return io
 
-    def solve_batch(self, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, out=None, stream=None, duals=True):
-        """Asynchronous on `stream` (default: torch's current stream).  Returns the dict of output tensors."""
+    def solve_batch(self, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, out=None, stream=None, duals=True,
+                    shift=None):
+        """Asynchronous on `stream` (default: torch's current stream).  Returns the dict of output tensors.
+        shift: dict(x0, xprev [B,N,9], uprev, uold, xy_send [B,N+1,2], hold int32 [B]) of CUDA tensors - the next DMPC
+        iteration's buffers, written by the solve's own epilogue (dmpc_solve_shift_batch; LPV_HP_N_main.py:102-117)."""
         torch = _torch()
         B, rows = x0.shape[0], xprev.shape[1]
         ins = dict(x0=x0, xprev=xprev, uprev=uprev, uold=uold, nbr_xy=nbr_xy, pose=pose, nbr_count=nbr_count)
@@ -122,7 +126,18 @@ class BatchedPlannerLPV(object):
         out = out if out is not None else self.alloc_outputs(B, duals)
         s = torch.cuda.current_stream(self.device) if stream is None else stream
         io = self._io(B, rows, ins, out, lambda t: None if t is None else t.data_ptr())
-        self._check(self.lib.dmpc_solve_batch(self._h, C.byref(io), C.c_void_p(s.cuda_stream)))
+        if shift is None:
+            self._check(self.lib.dmpc_solve_batch(self._h, C.byref(io), C.c_void_p(s.cuda_stream)))
+            return out
+        shapes = dict(x0=(B, 9), xprev=(B, self.N, 9), uprev=(B, self.N, 2), uold=(B, 2), xy_send=(B, self.N + 1, 2), hold=(B,))
+        sh = DmpcShiftIO()
+        for k, shp in shapes.items():
+            t = shift[k]
+            want = torch.int32 if k == "hold" else torch.float64
+            if not (t.is_cuda and t.dtype == want and t.is_contiguous() and tuple(t.shape) == shp):
+                raise DmpcError("shift[%s] must be a contiguous CUDA %s tensor of shape %s" % (k, want, shp))
+            setattr(sh, k, t.data_ptr())
+        self._check(self.lib.dmpc_solve_shift_batch(self._h, C.byref(io), C.byref(sh), C.c_void_p(s.cuda_stream)))
         return out
 
     # ---- host path (numpy in / numpy out; H2D + solve + D2H inside the C call) -----------------------------
@@ -149,6 +164,15 @@ class BatchedPlannerLPV(object):
         p = lambda t: None if t is None else t.data_ptr()
         self._check(self.lib.dmpc_shift_pack(self._h, z.shape[0], p(z), p(x0), p(xprev), p(uprev), p(uold), p(xy_send),
                                              C.c_void_p(s.cuda_stream)))
+
+    def shift_pack_hold(self, z, status, x0, xprev, uprev, uold, xy_send, hold, stream=None):
+        """shift_pack with the reference's stop rule (LPV_HP_N_main.py:102-104): QPs whose status is not feasible keep their
+        buffers (last valid plan) and count in `hold`."""
+        torch = _torch()
+        s = torch.cuda.current_stream(self.device) if stream is None else stream
+        p = lambda t: None if t is None else t.data_ptr()
+        self._check(self.lib.dmpc_shift_pack_hold(self._h, z.shape[0], p(z), p(status), p(x0), p(xprev), p(uprev), p(uold),
+                                                  p(xy_send), p(hold), C.c_void_p(s.cuda_stream)))
 
     def gather_neighbours(self, xy_all, nbr_idx, nbr_xy, pose, S, A_total, A_local, agent_offset, stream=None):
         torch = _torch()

@@ -59,8 +59,9 @@ typedef struct dmpc_options {
                              rounds + 2x one-change rounds; generic engine / singular S: that many penalty rounds)   */
   int32_t pdas_after;     /* active-set polish rounds after each interior-point phase, 2               */
   int32_t ipm_max_iter;   /* interior-point iteration cap per phase, 60                                */
-  int32_t engine;         /* 0 auto, 1 generic engine (any horizon, global spill), 2 fast engine (workspace packed in
-                             shared memory; dmpc_create fails if the horizon does not fit)                     */
+  int32_t engine;         /* dmpc_engine: 0 auto (the stage-wise engine), 2 condensed engine (workspace packed in shared memory;
+                             dmpc_create fails if the horizon does not fit; QPs whose condensed Hessian cannot be factorised
+                             are re-solved stage-wise in the same call), 3 stage-wise engine (any horizon)           */
   int32_t order_hint;     /* fast engine: 1 = a call orders and splits its launch by what the previous call of the same
                              batch size spent on each QP index (most expensive first, the interior-point ones alone on
                              an SM; consecutive MPC steps are alike).  Scheduling only: results are independent of it.
@@ -83,7 +84,9 @@ enum dmpc_status {
   DMPC_UNSOLVED = -10           /* numerical breakdown (NaN in the condensed factorisation): no verdict on the QP         */
 };
 
-enum dmpc_engine { DMPC_ENGINE_AUTO = 0, DMPC_ENGINE_GENERIC = 1, DMPC_ENGINE_FAST = 2 };
+/* DMPC_ENGINE_STAGE: uncondensed QP, Riccati sweeps over the stages, one warp per QP, O(N) shared memory (qp3_*.cuh).
+ * DMPC_ENGINE_FAST:  condensed QP, dense 2N x 2N factorisations, one 4-warp CTA per QP (qp2_*.cuh); horizons up to ~40. */
+enum dmpc_engine { DMPC_ENGINE_AUTO = 0, DMPC_ENGINE_FAST = 2, DMPC_ENGINE_STAGE = 3 };
 
 enum dmpc_error {
   DMPC_OK = 0,
@@ -117,6 +120,20 @@ typedef struct dmpc_batch_io {
   int32_t* pivots;           /* [B]                   active-set polish rounds used                      */
 } dmpc_batch_io;
 
+/* Buffers of the NEXT DMPC iteration, written by the solve's own epilogue (dmpc_solve_shift_batch): the caller's
+ * bookkeeping of planner/scripts/LPV_HP_N_main.py:102-117 and LPV_Planner.py:179-180.  A pointer may alias the same
+ * input of the call (x0 / xprev with xprev_rows == N / uprev / uold): a QP only ever touches its own rows. */
+typedef struct dmpc_shift_io {
+  double* x0;        /* [B,9]      <- xPred[1]                              LPV_HP_N_main.py:106 */
+  double* xprev;     /* [B,N,9]    <- xPred[1:]                             :114-115             */
+  double* uprev;     /* [B,N,2]    <- uPred, not shifted                    :113                 */
+  double* uold;      /* [B,2]      <- uPred[0]                              LPV_Planner.py:179-180 */
+  double* xy_send;   /* [B,N+1,2]  <- xPred[:,7:9], packed for the exchange LPV_HP_N_main.py:117 */
+  int32_t* hold;     /* [B] in/out: consecutive failed solves of this QP.  feasible (LPV_Planner.py:246-248) -> 0 and the
+                        buffers above receive this call's plan; otherwise +1 and the buffers keep the last valid plan (the
+                        reference breaks its loop here, LPV_HP_N_main.py:102-104; the caller reads hold to stop the scenario) */
+} dmpc_shift_io;
+
 typedef struct dmpc_handle dmpc_handle;
 
 void dmpc_default_options(dmpc_options* opt);
@@ -133,6 +150,10 @@ int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt);
  * `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  Asynchronous. */
 int dmpc_solve_batch(dmpc_handle* h, const dmpc_batch_io* io, void* stream);
 
+/* dmpc_solve_batch + the caller's bookkeeping fused into the solve kernel's epilogue (all six pointers of `next`
+ * required, DEVICE buffers): what dmpc_solve_batch followed by dmpc_shift_pack_hold leaves, in one launch. */
+int dmpc_solve_shift_batch(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_io* next, void* stream);
+
 /* Same call with HOST buffers (the end-to-end path).  Synchronous.  Pageable buffers: copied to page-locked staging,
  * H2D, solve, D2H.  If every buffer of the call is page-locked (cudaHostAlloc / cudaHostRegister) and
  * dmpc_options.host_direct = 1 (default) the kernel reads and writes them in place over PCIe - no staging copies,
@@ -145,6 +166,13 @@ int dmpc_solve_batch_host(dmpc_handle* h, const dmpc_batch_io* io);
  * z is [B,16N+12]; outputs may alias nothing in z. */
 int dmpc_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, double* d_x0, double* d_xprev /*[B,N,9]*/,
                     double* d_uprev, double* d_uold, double* d_xy_send /*[B,N+1,2]*/, void* stream);
+
+/* dmpc_shift_pack with the reference's stop rule (LPV_HP_N_main.py:102-104): d_status [B] of the solve that produced
+ * d_z, d_hold [B] in/out.  A QP whose status is feasible (1, 2, -2) is shifted and its hold reset to 0; any other
+ * status leaves all five buffers of that QP untouched (last valid plan) and increments its hold.  Nothing non-finite
+ * can reach the exchange through this call. */
+int dmpc_shift_pack_hold(dmpc_handle* h, int32_t B, const double* d_z, const int32_t* d_status, double* d_x0,
+                         double* d_xprev, double* d_uprev, double* d_uold, double* d_xy_send, int32_t* d_hold, void* stream);
 
 /* After the exchange: gathers each agent's neighbour trajectories and its own pose from the all-gathered buffer.
  * xy_all has the layout ncclAllGather leaves behind when every rank sends its xy_send [S, A_local, N+1, 2]:
@@ -185,7 +213,7 @@ int dmpc_ocd_lambda_update(dmpc_handle* h, int32_t S, int32_t A, double alpha, d
 int dmpc_ocd_lambda_update_hp(dmpc_handle* h, int32_t S, int32_t A, double alpha, double dth, const double* d_xy,
                               const double* d_planes, double* d_lambdas, void* stream);
 
-/* Engine the handle runs on: DMPC_ENGINE_GENERIC or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
+/* Engine the handle runs on: DMPC_ENGINE_STAGE or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
 int dmpc_engine(const dmpc_handle* h);
 
 /* Number of kernels the handle has launched so far (bench.py's gpu_launches claim). */
