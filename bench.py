@@ -196,7 +196,7 @@ def run_gpu(args):
     if single:
         A = 3
         S = (BATCH + A - 1) // A
-        eng = BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=NN, max_batch=S * A)
+        eng = BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=NN, max_batch=S * A, options={"engine": args.engine, "warm_start": args.warm})
         ins = steady_state_inputs(lambda **kw: eng.solve_batch_host(duals=False, **kw), BATCH, cfg, track, A=A)
         d_in = {k: torch.from_numpy(v).to(dev) for k, v in ins.items()}
         d_out = eng.alloc_outputs(BATCH, duals=False)
@@ -207,7 +207,7 @@ def run_gpu(args):
         par = "1 GPU, one CTA per QP"
     else:
         A, S = 16, 256 * world
-        eng = BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=NN, max_batch=S * A // world)
+        eng = BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=NN, max_batch=S * A // world, options={"engine": args.engine, "warm_start": args.warm})
         x0, xprev, uprev = sc.platoon_scenarios(S, A, HORIZON, cfg["dt"], track, seed0=0)
         idx, cnt = sc.topology(A, "chain", nn=NN)
         dm = ShardedDMPC(eng, S, A, idx, cnt, x0, xprev, uprev, rank=rank, world=world)
@@ -309,7 +309,7 @@ def run_gpu(args):
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "lpv_qp_fast_kernel" if eng.fast else "lpv_qp_solve_kernel", "kernel_ms": kern_ms,
+                "traffic": traffic, "kernel": "lpv_qp_fast_kernel" if eng.fast else "lpv_qp_stage_kernel", "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_qp": b_in + b_out,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback",
                 "note": "compulsory HBM traffic is 6.6 KB/QP; the kernel is bound by on-chip FP64 work (DESIGN.md), "
@@ -400,6 +400,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--warm", type=int, default=1, help="dmpc_options.warm_start")
+    ap.add_argument("--engine", type=int, default=0, help="dmpc_options.engine: 0 auto (stage-wise), 2 condensed, 3 stage-wise")
     ap.add_argument("--settle", type=int, default=30, help="DMPC workload: closed-loop iterations before warm-up")
     ap.add_argument("--workload", default="batch", choices=["batch", "dmpc"],
                     help="N=1 only: 'dmpc' runs the multi-GPU step (16-agent platoons, closed loop) on one GPU")

@@ -39,6 +39,7 @@ class DmpcOptions(C.Structure):
         ("polish_delta", C.c_double), ("cert_tol", C.c_double), ("ipm_mu0", C.c_double),
         ("polish_refine", C.c_int32), ("pdas_first", C.c_int32), ("pdas_after", C.c_int32),
         ("ipm_max_iter", C.c_int32), ("engine", C.c_int32), ("order_hint", C.c_int32), ("host_direct", C.c_int32),
+        ("warm_start", C.c_int32),
     ]
 
 

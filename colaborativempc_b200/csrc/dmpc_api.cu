@@ -24,6 +24,8 @@ struct dmpc_handle {
   double* d_gws;
   int *d_cost, *d_order;  // fast engine: per-QP cost of the last call and the launch order derived from it
   int order_B;            // batch size d_order is valid for (0: none yet)
+  unsigned char* d_warm;  // stage-wise engine: certified working set per QP of the last call ([max_batch][rows] bytes)
+  int warm_B;             // batch size d_warm belongs to (0: none yet)
   int nsm;                // SMs of the device
   size_t smem_alone;      // dynamic shared memory request that keeps a CTA alone on its SM
   cudaStream_t host_stream;  // dmpc_solve_batch_host
@@ -51,7 +53,7 @@ extern "C" void dmpc_default_options(dmpc_options* o) {
   if (!o) return;
   o->polish_delta = 1e-9; o->cert_tol = 1e-9; o->ipm_mu0 = 1e-6;
   o->polish_refine = 4; o->pdas_first = 4; o->pdas_after = 2; o->ipm_max_iter = 60;
-  o->engine = DMPC_ENGINE_AUTO; o->order_hint = 1; o->host_direct = 1;
+  o->engine = DMPC_ENGINE_AUTO; o->order_hint = 1; o->host_direct = 1; o->warm_start = 1;
 }
 
 static void apply_options(dmpc_handle* h) {
@@ -62,7 +64,8 @@ static void apply_options(dmpc_handle* h) {
 
 static bool options_ok(const dmpc_options* o) {
   return o->polish_delta > 0 && o->polish_delta < 1e-3 && o->cert_tol > 0 && o->ipm_mu0 > 0 && o->polish_refine >= 0 &&
-         o->polish_refine <= 32 && o->pdas_first >= 0 && o->pdas_after >= 1 && o->ipm_max_iter >= 1 && (o->engine == DMPC_ENGINE_AUTO || o->engine == DMPC_ENGINE_FAST || o->engine == DMPC_ENGINE_STAGE);
+         o->polish_refine <= 32 && o->pdas_first >= 0 && o->pdas_after >= 1 && o->ipm_max_iter >= 1 && (o->engine == DMPC_ENGINE_AUTO || o->engine == DMPC_ENGINE_FAST || o->engine == DMPC_ENGINE_STAGE) &&
+         o->warm_start >= 0 && o->warm_start <= 2;
 }
 
 static bool psd(const double* M, int n, bool strict) {  // LDL' without pivoting on the symmetrised matrix
@@ -144,11 +147,12 @@ extern "C" int dmpc_create(const dmpc_params* p, const dmpc_options* opt, int32_
     h->gws_stride = (long long)((stage_park_doubles(P.N, P.nn) + 1) & ~(size_t)1);
     CUDA_TRY(h, cudaMalloc(&h->d_gws, (size_t)h->gws_stride * sizeof(double) * max_batch));
     CUDA_TRY(h, cudaFuncSetAttribute(lpv_qp_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->stage_smem));
+    CUDA_TRY(h, cudaMalloc(&h->d_warm, (size_t)max_batch * (size_t)(P.N * (8 + P.nn))));
   }
+  CUDA_TRY(h, cudaMalloc(&h->d_cost, sizeof(int) * (size_t)max_batch));
+  CUDA_TRY(h, cudaMalloc(&h->d_order, sizeof(int) * ((size_t)max_batch + 1)));  // [max_batch]: expensive-QP count
   if (h->fast) {
     h->smem_bytes = sb2;
-    CUDA_TRY(h, cudaMalloc(&h->d_cost, sizeof(int) * (size_t)max_batch));
-    CUDA_TRY(h, cudaMalloc(&h->d_order, sizeof(int) * ((size_t)max_batch + 1)));  // [max_batch]: expensive-QP count
     // alone on the SM: a second CTA of this kernel (sb2 + 1 KB system share each) must not fit beside it
     const size_t per_sm = (size_t)optin + 1024;
     h->smem_alone = per_sm > 2 * (sb2 + 1024) ? per_sm - (sb2 + 1024) - 1024 + 16 : sb2;
@@ -164,6 +168,7 @@ extern "C" void dmpc_destroy(dmpc_handle* h) {
   if (h->d_gws) cudaFree(h->d_gws);
   if (h->d_cost) cudaFree(h->d_cost);
   if (h->d_order) cudaFree(h->d_order);
+  if (h->d_warm) cudaFree(h->d_warm);
   if (h->host_stream) cudaStreamDestroy(h->host_stream);
   if (h->d_stage) cudaFree(h->d_stage);
   delete h;
@@ -212,8 +217,25 @@ static int solve_impl(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_
   bp.gws = h->d_gws; bp.gws_stride = h->gws_stride;
   if (!h->fast) {
     if (next) { bp.nx_x0 = next->x0; bp.nx_xprev = next->xprev; bp.nx_uprev = next->uprev; bp.nx_uold = next->uold; bp.nx_xy = next->xy_send; bp.hold = next->hold; }
+    // cost-ordered launch (dmpc_options.order_hint): CTA i solves the QP that was i-th most expensive in the previous
+    // call of the same batch size - consecutive MPC steps of a scenario are alike - so the interior-point QPs (8x the mean
+    // work) start in the first wave instead of being the tail of the grid.  Scheduling only; results do not change.
+    const bool hint = h->opt.order_hint != 0;
+    if (hint) { bp.cost = h->d_cost; if (h->order_B == io->B) bp.order = h->d_order; }
+    if (h->opt.warm_start) {  // the previous call's certified working sets are this call's first guesses
+      if (h->warm_B != io->B) {
+        CUDA_TRY(h, cudaMemsetAsync(h->d_warm, 0, (size_t)io->B * (size_t)(h->P.N * (8 + h->P.nn)), st));
+        h->warm_B = io->B;
+      }
+      bp.warm = h->d_warm; bp.warm_shift = h->opt.warm_start == 2;
+    }
     lpv_qp_stage_kernel<<<io->B, QP3_THREADS, h->stage_smem, st>>>(h->P, bp);
     h->launches++;
+    if (hint) {
+      order_by_cost_kernel<<<1, ORDER_THREADS, 0, st>>>(h->d_cost, h->d_order, h->d_order + h->max_batch, io->B, h->nsm);
+      h->order_B = io->B;
+      h->launches++;
+    }
     CUDA_TRY(h, cudaGetLastError());
     return DMPC_OK;
   }

@@ -303,6 +303,10 @@ __global__ void __launch_bounds__(QP_THREADS, 4) lpv_qp_fast_kernel(const __grid
 #define ORDER_THREADS 1024
 #define ORDER_CLASSES 8
 __device__ __forceinline__ int cost_class(int cst) {
+  if (cst & (1 << 20)) {  // stage-wise engine: 3 factorisations + solves; one active-set round ~ 5, an interior-point solve ~ 80
+    cst &= (1 << 20) - 1;  // (bit 21: interior point used)
+    return cst >= 110 ? 7 : cst >= 80 ? 6 : cst >= 50 ? 5 : cst >= 30 ? 4 : cst >= 20 ? 3 : cst >= 12 ? 2 : cst >= 7 ? 1 : 0;
+  }
   return cst >= 24 * 16 ? 7 : cst >= 24 ? 6 : cst >= 12 ? 5 : cst >= 6 ? 4 : cst >= 4 ? 3 : cst >= 3 ? 2 : cst >= 2 ? 1 : 0;
 }
 

@@ -81,19 +81,24 @@ struct Hdr3 {
   int refine, pdas_first, pdas_after, ipm_max;
   int n_rounds, n_ipm, n_fact, n_solve;
   double delta, cert_tol, ipm_mu0;
-  double Q2[81];      // 2 Q   (P = 2 blockdiag(...), LPV_Planner.py:399-410)
   double Qs2[9];      // 2 Qs
   double R2[4], dR2[4];
   double q0;          // 2 * (-vx_ref Q[0,0])   (LPV_Planner.py:412)
   double lim[6];      // min_vel max_vel max_rs max_ls max_ac max_dc
   double mind;        // min_dist
   double x0[9], uold[2];
-  // cost-to-go and the per-stage temporaries of the Riccati passes
-  double Pxx[81], Pvx[18], Pvv[4], px[2][9], pv[2][2];
-  double MA[27], G[18], ev[9], fv[2], TA[9], Fs[6], Huu[4], hu[2], Apx[9];
-  double fx[2][9], fu[2][2];   // forward sweep: the step of the running stage (ping-pong)
-  unsigned long long hist[16];
+  int nq;                   // nonzeros of the upper triangle of 2 Q (P = 2 blockdiag(...), LPV_Planner.py:399-410)
+  double Q2u[45];           // 2 Q at the 45 upper-triangle pairs (tri order)
+  // cost-to-go and the per-stage temporaries of the Riccati passes (layout: see ric_factor_backward3)
+  double Pf[99];            // [Pxx (9 x 9); Pvx (2 x 9)], row stride 9 (bank-conflict free for one row per lane pair)
+  double Pvv[4], px[2][9], pv[2][2], pe[9];
+  double Y[44], Yb[22];     // Pf [Acol | d] (11 x 4),  Pf [b0 | b1] (11 x 2)
+  double TA[9], Apx[3], Fc[18];
+  double dbuf[2][9];        // dynamics defect of the stage being processed / the next one
+  unsigned long long hist[8];
   unsigned char tri[48];  // (i << 4) | j of the 45 upper-triangle pairs of a 9 x 9 matrix
+  unsigned char wix[48];  // index into the stage's Weff of pair e (outputs 0, 3, 7, 8), 255 = none
+  unsigned char nzl[48];  // the nq pairs e with 2 Q != 0
 };
 
 struct Ctx3 {
@@ -101,8 +106,9 @@ struct Ctx3 {
   Hdr3* hd;
   double *Acol, *Bcol, *ax, *ay, *mx, *my, *eyb, *pxy;   // problem data (mx, my: midpoint ego-neighbour, on the plane)
   double *x, *u, *sig, *lam, *tt;                         // iterate: x[k] = x_{k+1}
-  double *dx, *du, *dsig, *dlam, *dtt;                    // direction (dx doubles as the dynamics defect on input)
-  double *gx, *gu, *gs;                                   // gradient handed to a solve
+  double *dx, *du, *dsig, *dlam, *dtt;                    // direction
+  double *gx, *gu, *gs;                                   // gradient handed to a solve: SAME storage as dx, du, dsig (the
+                                                          // forward sweep overwrites stage k's gradient with stage k's step)
   double *D, *res;                                        // row weights, row residuals
   double *F, *Wi, *zk, *Si, *bh, *Weff;                   // Riccati factor per stage, slack elimination per stage
   unsigned short* rinfo;                                  // row j -> (k << 7) | r
@@ -123,7 +129,7 @@ Q3HD size_t carve_workspace3(Ctx3& c, char* sm, int N, int nn) {
   c.eyb = take(n); c.pxy = take(2 * n);
   c.x = take(9 * n); c.u = take(2 * n); c.sig = take(3 * n); c.lam = take(RT); c.tt = take(RT);
   c.dx = take(9 * n); c.du = take(2 * n); c.dsig = take(3 * n); c.dlam = take(RT); c.dtt = take(RT);
-  c.gx = take(9 * n); c.gu = take(2 * n); c.gs = take(3 * n);
+  c.gx = c.dx; c.gu = c.du; c.gs = c.dsig;
   c.D = take(RT); c.res = take(RT);
   c.F = take(18 * n); c.Wi = take(4 * n); c.zk = take(2 * n);
   c.Si = take(6 * n); c.bh = take(4 * n); c.Weff = take(10 * n);
@@ -183,7 +189,11 @@ Q3D void build_tables3(const Ctx3& c) {
   Q3_FOR(e, 45) {
     int i = 0, rem = e;
     while (rem >= 9 - i) { rem -= 9 - i; ++i; }
-    c.hd->tri[e] = (unsigned char)((i << 4) | (i + rem));
+    const int j = i + rem;
+    c.hd->tri[e] = (unsigned char)((i << 4) | j);
+    const int a = i == 0 ? 0 : (i == 3 ? 1 : (i == 7 ? 2 : (i == 8 ? 3 : -1)));
+    const int b = j == 0 ? 0 : (j == 3 ? 1 : (j == 7 ? 2 : (j == 8 ? 3 : -1)));
+    c.hd->wix[e] = (a >= 0 && b >= 0) ? (unsigned char)(a * 4 - ((a * (a - 1)) >> 1) + (b - a)) : (unsigned char)255;
   }
 }
 
@@ -208,9 +218,27 @@ Q3D double row_res3(const Ctx3& c, int j) {
   return fma(c.ax[i], xk[7] - c.mx[i], c.ay[i] * (xk[8] - c.my[i])) + (0.5 * c.hd->mind - sk[2]);
 }
 
-// res_j at the current iterate; invalid rows (unused neighbour slots) read -1.
+// res_j at the current iterate, one lane per stage (straight-line code: no per-row decoding); invalid rows (unused
+// neighbour slots) read -1.  Ends with a barrier.
 Q3D void eval_residuals3(const Ctx3& c) {
-  Q3_FOR(j, c.RT) c.res[j] = row_ok3(c, j) ? row_res3(c, j) : -1.0;
+  const double* lim = c.hd->lim;
+  const double hm = 0.5 * c.hd->mind;
+  Q3_FOR(k, c.N) {
+    const double* xk = c.x + 9 * k;
+    const double* sk = c.sig + 3 * k;
+    double* r = c.res + k * c.rst;
+    r[0] = lim[0] - xk[0];
+    r[1] = (xk[0] - lim[1]) + sk[0];
+    r[2] = (xk[3] - c.eyb[k]) + sk[1];
+    r[3] = (-xk[3] - c.eyb[k]) + sk[1];
+    for (int i = 0; i < c.nn; ++i) {
+      const int q = k * c.nn + i;
+      r[4 + i] = i < c.cnt ? fma(c.ax[q], xk[7] - c.mx[q], c.ay[q] * (xk[8] - c.my[q])) + (hm - sk[2]) : -1.0;
+    }
+    double* rb = c.res + c.Rs + 4 * k;
+    const double u0 = c.u[2 * k], u1 = c.u[2 * k + 1];
+    rb[0] = u0 - lim[2]; rb[1] = -u0 - lim[3]; rb[2] = u1 - lim[4]; rb[3] = -u1 - lim[5];
+  }
   Q3_SYNC();
 }
 
@@ -330,7 +358,8 @@ Q3D double arow3(const double* A, const double* v, int j) {
 }
 // (B_k du)_j
 Q3D double brow3(const double* B, double d0, double d1, int j) {
-  return j == 0 ? fma(B[0], d0, B[3] * d1) : (j == 1 ? B[1] * d0 : (j == 2 ? B[2] * d0 : 0.0));
+  const double b0 = j < 3 ? B[j] : 0.0, b1 = j == 0 ? B[3] : 0.0;
+  return fma(b0, d0, b1 * d1);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -371,41 +400,35 @@ Q3D void stage_weights3(const Ctx3& c) {
   }
 }
 
-// Hessian entry (i, j), i <= j, of the state x_{k+1}: 2Q + S' Weff_k S with S = rows (0, 3, 7, 8)
-Q3D double qt3(const Ctx3& c, int k, int i, int j) {
-  double v = c.hd->Q2[i * 9 + j];
-  const int a = i == 0 ? 0 : (i == 3 ? 1 : (i == 7 ? 2 : (i == 8 ? 3 : -1)));
-  const int b = j == 0 ? 0 : (j == 3 ? 1 : (j == 7 ? 2 : (j == 8 ? 3 : -1)));
-  if (a >= 0 && b >= 0) v += c.Weff[10 * k + a * 4 - ((a * (a - 1)) >> 1) + (b - a)];
-  return v;
+// Hessian entry of the state x_{k+1} at upper-triangle pair e: 2Q + S' Weff_k S with S = rows (0, 3, 7, 8)
+Q3D double qt3(const Ctx3& c, int k, int e) {
+  const int w = c.hd->wix[e];
+  return w != 255 ? c.hd->Q2u[e] + c.Weff[10 * k + w] : c.hd->Q2u[e];
 }
 
-// What a solve's gradient is made of.  Always: row term C'w with the per-row w of the mode.
-//   G3_ALM   cost gradient + w = lam + D res              (method-of-multipliers polish pass)
-//   G3_AFF   cost gradient + w = D (res + t)              (interior point, predictor; lam cancels)
-//   G3_COR   w = (smu - dtt dlam) / t only                (interior point, corrector increment; dtt/dlam = affine step)
-//   G3_LAG   cost gradient + w = lam                      (Lagrangian gradient: the costate pass)
+// What a solve's gradient is made of: cost gradient + C'w with the per-row w of the mode.
+//   G3_ALM   w = lam + D res                                       (method-of-multipliers polish pass)
+//   G3_AFF   w = D (res + t)                                       (interior point, predictor; lam cancels)
+//   G3_COR   w = D (res + t) + (smu - dtt dlam) / t                (interior point, corrector; dtt/dlam = affine step)
+//   G3_LAG   w = lam                                               (Lagrangian gradient: the costate pass)
 enum { G3_ALM = 0, G3_AFF = 1, G3_COR = 2, G3_LAG = 3 };
 
 Q3D double row_w3(const Ctx3& c, int j, int mode, double smu) {
   if (mode == G3_ALM) return fma(c.D[j], c.res[j], c.lam[j]);
   if (mode == G3_AFF) return c.D[j] * (c.res[j] + c.tt[j]);
-  if (mode == G3_COR) return (smu - c.dtt[j] * c.dlam[j]) / c.tt[j];
+  if (mode == G3_COR) return fma(c.D[j], c.res[j] + c.tt[j], (smu - c.dtt[j] * c.dlam[j]) / c.tt[j]);
   return c.lam[j];
 }
 
-// Gradient of the solve (c.gx, c.gu, c.gs), slack part folded into gx through the stage's Si / bh (stage_weights3 of the
-// current D must have run), and - with `defects` - the dynamics defects d_k = A_k x_k + B_k u_k - x_{k+1} into c.dx
-// (zeros otherwise).  G3_COR is an INCREMENT on top of the predictor: c.gs accumulates (the slack steps are recomputed from
-// the totals) and c.dx keeps the predictor's step.  One lane per stage.  Ends with a barrier.
-Q3D void assemble_gradient3(const Ctx3& c, int mode, double smu, int defects) {
+// Gradient of the solve into c.gx / c.gu / c.gs (= the direction's storage), slack part folded into gx through the
+// stage's Si / bh (stage_weights3 of the current D must have run).  One lane per stage.  Ends with a barrier.
+Q3D void assemble_gradient3(const Ctx3& c, int mode, double smu) {
   const Hdr3* hd = c.hd;
   Q3_FOR(k, c.N) {
     const double* xk1 = c.x + 9 * k;
     const double* sk = c.sig + 3 * k;
     const double* uk = c.u + 2 * k;
     const int j0 = k * c.rst, jb = c.Rs + 4 * k;
-    // row terms
     const double w0 = row_w3(c, j0, mode, smu), w1 = row_w3(c, j0 + 1, mode, smu);
     const double w2 = row_w3(c, j0 + 2, mode, smu), w3 = row_w3(c, j0 + 3, mode, smu);
     double wx = 0.0, wy = 0.0, ws = 0.0;
@@ -413,232 +436,191 @@ Q3D void assemble_gradient3(const Ctx3& c, int mode, double smu, int defects) {
       const double wi = row_w3(c, j0 + 4 + i, mode, smu);
       wx = fma(c.ax[k * c.nn + i], wi, wx); wy = fma(c.ay[k * c.nn + i], wi, wy); ws += wi;
     }
-    double g[9], s[3], gu0, gu1;
-    if (mode == G3_COR) {
-      for (int i = 0; i < 9; ++i) g[i] = 0.0;
-      s[0] = s[1] = s[2] = 0.0; gu0 = gu1 = 0.0;
-    } else {
-      for (int i = 0; i < 9; ++i) {
-        double a = 0.0;
-        for (int l = 0; l < 9; ++l) a = fma(hd->Q2[i * 9 + l], xk1[l], a);
-        g[i] = a;
-      }
-      g[0] += hd->q0;
-      g[7] += 2.0 * c.pxy[2 * k]; g[8] += 2.0 * c.pxy[2 * k + 1];
-      for (int i = 0; i < 3; ++i) s[i] = hd->Qs2[i * 3] * sk[0] + hd->Qs2[i * 3 + 1] * sk[1] + hd->Qs2[i * 3 + 2] * sk[2];
-      const double* um = k > 0 ? uk - 2 : hd->uold;
-      const double d0 = uk[0] - um[0], d1 = uk[1] - um[1];
-      gu0 = hd->R2[0] * uk[0] + hd->R2[1] * uk[1] + hd->dR2[0] * d0 + hd->dR2[1] * d1;
-      gu1 = hd->R2[2] * uk[0] + hd->R2[3] * uk[1] + hd->dR2[2] * d0 + hd->dR2[3] * d1;
-      if (k < c.N - 1) {
-        const double e0 = uk[2] - uk[0], e1 = uk[3] - uk[1];
-        gu0 -= hd->dR2[0] * e0 + hd->dR2[1] * e1;
-        gu1 -= hd->dR2[2] * e0 + hd->dR2[3] * e1;
-      }
+    double* g = c.gx + 9 * k;
+    for (int i = 0; i < 9; ++i) g[i] = 0.0;
+    for (int q = 0; q < hd->nq; ++q) {
+      const int e = hd->nzl[q], i = hd->tri[e] >> 4, j = hd->tri[e] & 15;
+      g[i] = fma(hd->Q2u[e], xk1[j], g[i]);
+      if (i != j) g[j] = fma(hd->Q2u[e], xk1[i], g[j]);
     }
-    g[0] += w1 - w0; g[3] += w2 - w3; g[7] += wx; g[8] += wy;
-    s[0] += w1; s[1] += w2 + w3; s[2] -= ws;
+    double s0 = hd->Qs2[0] * sk[0] + hd->Qs2[1] * sk[1] + hd->Qs2[2] * sk[2] + w1;
+    double s1 = hd->Qs2[3] * sk[0] + hd->Qs2[4] * sk[1] + hd->Qs2[5] * sk[2] + w2 + w3;
+    double s2 = hd->Qs2[6] * sk[0] + hd->Qs2[7] * sk[1] + hd->Qs2[8] * sk[2] - ws;
+    const double* um = k > 0 ? uk - 2 : hd->uold;
+    const double d0 = uk[0] - um[0], d1 = uk[1] - um[1];
+    double gu0 = hd->R2[0] * uk[0] + hd->R2[1] * uk[1] + hd->dR2[0] * d0 + hd->dR2[1] * d1;
+    double gu1 = hd->R2[2] * uk[0] + hd->R2[3] * uk[1] + hd->dR2[2] * d0 + hd->dR2[3] * d1;
+    if (k < c.N - 1) {
+      const double e0 = uk[2] - uk[0], e1 = uk[3] - uk[1];
+      gu0 -= hd->dR2[0] * e0 + hd->dR2[1] * e1;
+      gu1 -= hd->dR2[2] * e0 + hd->dR2[3] * e1;
+    }
     gu0 += row_w3(c, jb, mode, smu) - row_w3(c, jb + 1, mode, smu);
     gu1 += row_w3(c, jb + 2, mode, smu) - row_w3(c, jb + 3, mode, smu);
     // slack elimination: the slack gradient reaches the outputs as -bh Si gs
     const double* si = c.Si + 6 * k;
     const double* bh = c.bh + 4 * k;
-    const double v0 = si[0] * s[0] + si[1] * s[1] + si[2] * s[2];
-    const double v1 = si[1] * s[0] + si[3] * s[1] + si[4] * s[2];
-    const double v2 = si[2] * s[0] + si[4] * s[1] + si[5] * s[2];
-    g[0] -= bh[0] * v0; g[3] -= bh[1] * v1; g[7] -= bh[2] * v2; g[8] -= bh[3] * v2;
-    for (int i = 0; i < 9; ++i) c.gx[9 * k + i] = g[i];
-    if (mode == G3_COR) { c.gs[3 * k] += s[0]; c.gs[3 * k + 1] += s[1]; c.gs[3 * k + 2] += s[2]; }
-    else { c.gs[3 * k] = s[0]; c.gs[3 * k + 1] = s[1]; c.gs[3 * k + 2] = s[2]; }
+    const double v0 = si[0] * s0 + si[1] * s1 + si[2] * s2;
+    const double v1 = si[1] * s0 + si[3] * s1 + si[4] * s2;
+    const double v2 = si[2] * s0 + si[4] * s1 + si[5] * s2;
+    g[0] += hd->q0 + (w1 - w0) - bh[0] * v0;
+    g[3] += (w2 - w3) - bh[1] * v1;
+    g[7] += 2.0 * c.pxy[2 * k] + wx - bh[2] * v2;
+    g[8] += 2.0 * c.pxy[2 * k + 1] + wy - bh[3] * v2;
+    c.gs[3 * k] = s0; c.gs[3 * k + 1] = s1; c.gs[3 * k + 2] = s2;
     c.gu[2 * k] = gu0; c.gu[2 * k + 1] = gu1;
-    if (mode == G3_COR) continue;
-    if (defects) {
-      const double* xk = k > 0 ? c.x + 9 * (k - 1) : hd->x0;
-      const double* A = c.Acol + 27 * k;
-      const double* B = c.Bcol + 4 * k;
-      for (int i = 0; i < 9; ++i) c.dx[9 * k + i] = arow3(A, xk, i) + brow3(B, uk[0], uk[1], i) - xk1[i];
-    } else {
-      for (int i = 0; i < 9; ++i) c.dx[9 * k + i] = 0.0;
-    }
   }
   Q3_SYNC();
 }
 
+// dynamics defect of stage k at the current iterate, component j:  (A_k x_k + B_k u_k - x_{k+1})_j
+Q3D double defect3(const Ctx3& c, int k, int j) {
+  const double* xk = k > 0 ? c.x + 9 * (k - 1) : c.hd->x0;
+  return arow3(c.Acol + 27 * k, xk, j) + brow3(c.Bcol + 4 * k, c.u[2 * k], c.u[2 * k + 1], j) - c.x[9 * k + j];
+}
+
+// one work item on the device = the lane with that index; on the host every item runs
+#ifdef QP3_HOST
+#define Q3_ITEM(l, n) for (int l = 0; l < (n); ++l)
+#define Q3_ITEMS(l, lo, hi) for (int l = (lo); l < (hi); ++l)
+#else
+#define Q3_ITEM(l, n) for (int l = Q3_LANE; l < (n); l += 32)
+#define Q3_ITEMS(l, lo, hi) for (int l = Q3_LANE; l >= (lo) && l < (hi); l += 32)
+#endif
+
 // ---------------------------------------------------------------------------------------------------
 // Riccati recursion.  Cost-to-go of the augmented state xi = (dx_k, dv_k = du_{k-1}) from stage k on, including the cost
-// of x_k itself:  W_k(xi) = 1/2 xi' [Pxx Pxv; Pvx Pvv] xi + (px, pv)' xi.  Stage k, with P+ = P_{k+1}, defect d_k:
+// of x_k itself:  W_k(xi) = 1/2 xi' [Pxx Pxv; Pvx Pvv] xi + (px, pv)' xi.  Stage k, with P+ = P_{k+1}, defect d_k, the
+// two columns b0 = (B0, B1, B2, 0..), b1 = (B3, 0..) of B_k and A_k = [Acol | e_3 .. e_8]:
 //   G   = B'Pxx+ + Pvx+                       (2 x 9)         Huu = Rt + dR2 + G B + B'Pxv+ + Pvv+
 //   F   = G A                                 (2 x 9)         hu  = gu + B'(px+ + Pxx+ d) + pv+ + Pvx+ d
 //   du  = -Huu^-1 (hu + F dx - dR2 dv)
 //   Pxx = A'Pxx+A - F'Huu^-1 F + Qt_{k-1}     Pvx = dR2 Huu^-1 F     Pvv = dR2 - dR2 Huu^-1 dR2
 //   px  = A'(px+ + Pxx+ d) - F'Huu^-1 hu + gx_{k-1}               pv  = dR2 Huu^-1 hu
-// A = I + (column block): A'Pxx+A needs MA = Pxx+ Acol (9 x 3) and TA = Acol'MA (3 x 3) only.
-// Kept per stage for later solves with the same weights: F (18), Huu^-1 (3), z = Huu^-1 hu (2).
-// Backward pass with factorisation.  In: c.gx/gu (gradient, slack part folded), c.dx (defects), c.D, c.Weff.
-Q3D void ric_factor_backward3(const Ctx3& c) {
+// Three phases per stage, every lane running the same code on a statically assigned item:
+//   1  Y = Pf [Acol | d] (11 x 4) and Yb = Pf [b0 | b1] (11 x 2), Pf = [Pxx+; Pvx+]: lane (r, h) holds row r of Pf in
+//      registers and produces two columns of Y and one of Yb;  pe = px+ + Pxx+ d
+//   2  TA = Acol' Y[0:9, 0:3] and Acol' pe (twelve 9-term products), F (18 short products); Huu, its inverse and
+//      z = Huu^-1 hu are computed by EVERY lane (uniform scalar code: no broadcast, no extra barrier)
+//   3  the 45 + 18 + 3 + 9 + 2 entries of P_k, p_k, and the defect of the next stage to be processed
+// Kept per stage for later solves with the same weights: F (18), Huu^-1 (3), z (2).
+// In: c.gx / c.gu (gradient, slack part folded), c.D (box rows), c.Weff.  defects: d_k from the iterate, else zero.
+Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
   Hdr3* hd = c.hd;
   const int N = c.N;
-  double* Pxx = hd->Pxx;
-  double* Pvx = hd->Pvx;
-  double* Pvv = hd->Pvv;
+  double* Pf = hd->Pf;
   double* px = hd->px[0];
   double* pv = hd->pv[0];
   const double* dR2 = hd->dR2;
-  Q3_FOR(e, 45) {
+  Q3_ITEM(e, 45) {
     const int ij = hd->tri[e], i = ij >> 4, j = ij & 15;
-    const double v = qt3(c, N - 1, i, j);
-    Pxx[i * 9 + j] = v; Pxx[j * 9 + i] = v;
+    const double v = qt3(c, N - 1, e);
+    Pf[i * 9 + j] = v; Pf[j * 9 + i] = v;
   }
-  Q3_FOR(e, 18) Pvx[e] = 0.0;
-  Q3_FOR(e, 4) Pvv[e] = 0.0;
-  Q3_FOR(e, 9) px[e] = c.gx[9 * (N - 1) + e];
-  Q3_FOR(e, 2) pv[e] = 0.0;
+  Q3_ITEM(e, 18) Pf[81 + e] = 0.0;
+  Q3_ITEM(e, 4) hd->Pvv[e] = 0.0;
+  Q3_ITEM(e, 9) { px[e] = c.gx[9 * (N - 1) + e]; hd->dbuf[(N - 1) & 1][e] = defects ? defect3(c, N - 1, e) : 0.0; hd->dbuf[N & 1][e] = 0.0; }
+  Q3_ITEM(e, 2) pv[e] = 0.0;
   Q3_SYNC();
 #pragma unroll 1
   for (int k = N - 1; k >= 0; --k) {
     const double* A = c.Acol + 27 * k;
     const double* B = c.Bcol + 4 * k;
-    const double* d = c.dx + 9 * k;
-    // ---- phase 1: everything that reads P+ only
-    Q3_FOR(it, 59) {
-      if (it < 27) {
-        const int i = it / 3, j = it - 3 * i;
-        double s0 = 0.0, s1 = 0.0;
+    const double* d = hd->dbuf[k & 1];
+    // ---- phase 1
+    Q3_ITEM(l, 22) {
+      const int r = l >> 1, h = l & 1;
+      double p[9];
 #pragma unroll
-        for (int l = 0; l < 8; l += 2) { s0 = fma(Pxx[i * 9 + l], A[l * 3 + j], s0); s1 = fma(Pxx[i * 9 + l + 1], A[(l + 1) * 3 + j], s1); }
-        s0 = fma(Pxx[i * 9 + 8], A[24 + j], s0);
-        hd->MA[it] = s0 + s1;
-      } else if (it < 45) {
-        const int e = it - 27, m = e / 9, j = e - 9 * m;
-        hd->G[e] = m == 0 ? fma(B[0], Pxx[j], fma(B[1], Pxx[9 + j], fma(B[2], Pxx[18 + j], Pvx[j])))
-                          : fma(B[3], Pxx[j], Pvx[9 + j]);
-      } else if (it < 54) {
-        const int i = it - 45;
-        double s0 = 0.0, s1 = 0.0;
+      for (int q = 0; q < 9; ++q) p[q] = Pf[r * 9 + q];
+      const double* z0p = A + 2 * h;            // column 2h of Acol, stride 3
+      const double* z1p = h ? d : A + 1;        // column 1 of Acol (stride 3) or the defect (stride 1)
+      const int st1 = h ? 1 : 3;
+      double a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
 #pragma unroll
-        for (int l = 0; l < 8; l += 2) { s0 = fma(Pxx[i * 9 + l], d[l], s0); s1 = fma(Pxx[i * 9 + l + 1], d[l + 1], s1); }
-        hd->ev[i] = fma(Pxx[i * 9 + 8], d[8], s0) + s1;
-      } else if (it < 56) {
-        const int m = it - 54;
-        double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-        for (int l = 0; l < 8; l += 2) { s0 = fma(Pvx[m * 9 + l], d[l], s0); s1 = fma(Pvx[m * 9 + l + 1], d[l + 1], s1); }
-        hd->fv[m] = fma(Pvx[m * 9 + 8], d[8], s0) + s1;
-      } else {
-        const int q = it - 56;  // Huu entries 00, 01, 11
-        const double* db = c.D + c.Rs + 4 * k;
-        // (Pxx+ b)_i for b = (B0, B1, B2, 0...) and the products with the two columns of B
-        const double pb0 = fma(Pxx[0], B[0], fma(Pxx[1], B[1], Pxx[2] * B[2]));
-        double v;
-        if (q == 0) {
-          const double pb1 = fma(Pxx[9], B[0], fma(Pxx[10], B[1], Pxx[11] * B[2]));
-          const double pb2 = fma(Pxx[18], B[0], fma(Pxx[19], B[1], Pxx[20] * B[2]));
-          const double bPb = fma(B[0], pb0, fma(B[1], pb1, B[2] * pb2));
-          const double pvb = fma(Pvx[0], B[0], fma(Pvx[1], B[1], Pvx[2] * B[2]));
-          v = hd->R2[0] + db[0] + db[1] + dR2[0] + bPb + 2.0 * pvb + Pvv[0];
-        } else if (q == 1) {
-          const double pvb10 = fma(Pvx[9], B[0], fma(Pvx[10], B[1], Pvx[11] * B[2]));  // (Pvx B)[1][0]
-          v = hd->R2[1] + dR2[1] + B[3] * pb0 + Pvx[0] * B[3] + pvb10 + Pvv[1];
-        } else {
-          v = hd->R2[3] + db[2] + db[3] + dR2[3] + B[3] * B[3] * Pxx[0] + 2.0 * Pvx[9] * B[3] + Pvv[3];
-        }
-        hd->Huu[q] = v;
+      for (int q = 0; q < 8; q += 2) {
+        a0 = fma(p[q], z0p[3 * q], a0); a1 = fma(p[q + 1], z0p[3 * q + 3], a1);
+        b0 = fma(p[q], z1p[st1 * q], b0); b1 = fma(p[q + 1], z1p[st1 * (q + 1)], b1);
       }
+      a0 = fma(p[8], z0p[24], a0) + a1;
+      b0 = fma(p[8], z1p[st1 * 8], b0) + b1;
+      hd->Y[r * 4 + 2 * h] = a0;
+      hd->Y[r * 4 + 2 * h + 1] = b0;
+      hd->Yb[r * 2 + h] = h ? B[3] * p[0] : fma(B[0], p[0], fma(B[1], p[1], B[2] * p[2]));
+      if (h && r < 9) hd->pe[r] = px[r] + b0;
     }
     Q3_SYNC();
-    // ---- phase 2
-    Q3_FOR(it, 24) {
-      if (it < 6) {  // TA upper triangle
-        const int i = it < 3 ? 0 : (it < 5 ? 1 : 2), j = it < 3 ? it : (it < 5 ? it - 2 : 2);
-        double s0 = 0.0, s1 = 0.0;
+    // ---- phase 2: scalar section, identical on every lane
+    const double* Yb = hd->Yb;
+    const double* db = c.D + c.Rs + 4 * k;
+    const double pe0 = hd->pe[0], pe1 = hd->pe[1], pe2 = hd->pe[2];
+    const double hu0 = c.gu[2 * k] + pv[0] + hd->Y[39] + fma(B[0], pe0, fma(B[1], pe1, B[2] * pe2));
+    const double hu1 = c.gu[2 * k + 1] + pv[1] + hd->Y[43] + B[3] * pe0;
+    const double H00 = hd->R2[0] + db[0] + db[1] + dR2[0] + fma(B[0], Yb[0], fma(B[1], Yb[2], B[2] * Yb[4])) + 2.0 * Yb[18] + hd->Pvv[0];
+    const double H01 = hd->R2[1] + dR2[1] + fma(B[0], Yb[1], fma(B[1], Yb[3], B[2] * Yb[5])) + Yb[19] + Yb[20] + hd->Pvv[1];
+    const double H11 = hd->R2[3] + db[2] + db[3] + dR2[3] + B[3] * Yb[1] + 2.0 * Yb[21] + hd->Pvv[3];
+    const double idet = 1.0 / (H00 * H11 - H01 * H01);
+    const double W00 = H11 * idet, W01 = -H01 * idet, W11 = H00 * idet;
+    const double z0 = W00 * hu0 + W01 * hu1, z1 = W01 * hu0 + W11 * hu1;
+    Q3_ITEM(l, 12) {
+      const int col = l < 9 ? l / 3 : l - 9;
+      const double* v = l < 9 ? hd->Y + (l % 3) : hd->pe;
+      const int sv = l < 9 ? 4 : 1;
+      double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-        for (int l = 0; l < 8; l += 2) { s0 = fma(A[l * 3 + i], hd->MA[l * 3 + j], s0); s1 = fma(A[(l + 1) * 3 + i], hd->MA[(l + 1) * 3 + j], s1); }
-        const double v = fma(A[24 + i], hd->MA[24 + j], s0) + s1;
-        hd->TA[i * 3 + j] = v; hd->TA[j * 3 + i] = v;
-      } else if (it < 12) {
-        const int e = it - 6, m = e / 3, j = e - 3 * m;
-        double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-        for (int l = 0; l < 8; l += 2) { s0 = fma(hd->G[m * 9 + l], A[l * 3 + j], s0); s1 = fma(hd->G[m * 9 + l + 1], A[(l + 1) * 3 + j], s1); }
-        hd->Fs[e] = fma(hd->G[m * 9 + 8], A[24 + j], s0) + s1;
-      } else if (it < 21) {
-        const int j = it - 12;
-        double v;
-        if (j < 3) {
-          double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-          for (int l = 0; l < 8; l += 2) { s0 = fma(A[l * 3 + j], px[l] + hd->ev[l], s0); s1 = fma(A[(l + 1) * 3 + j], px[l + 1] + hd->ev[l + 1], s1); }
-          v = fma(A[24 + j], px[8] + hd->ev[8], s0) + s1;
-        } else {
-          v = px[j] + hd->ev[j];
-        }
-        hd->Apx[j] = v;
-      } else if (it < 23) {
-        const int m = it - 21;
-        const double p0 = px[0] + hd->ev[0];
-        double v = c.gu[2 * k + m] + pv[m] + hd->fv[m];
-        if (m == 0) v += fma(B[0], p0, fma(B[1], px[1] + hd->ev[1], B[2] * (px[2] + hd->ev[2])));
-        else v = fma(B[3], p0, v);
-        hd->hu[m] = v;
-      } else {
-        const double h00 = hd->Huu[0], h01 = hd->Huu[1], h11 = hd->Huu[2];
-        const double idet = 1.0 / (h00 * h11 - h01 * h01);
-        double* W = c.Wi + 4 * k;
-        W[0] = h11 * idet; W[1] = -h01 * idet; W[2] = h00 * idet;
-      }
+      for (int q = 0; q < 8; q += 2) { a0 = fma(A[3 * q + col], v[sv * q], a0); a1 = fma(A[3 * q + 3 + col], v[sv * (q + 1)], a1); }
+      a0 = fma(A[24 + col], v[sv * 8], a0) + a1;
+      if (l < 9) hd->TA[l] = a0; else hd->Apx[l - 9] = a0;
     }
+    Q3_ITEMS(l, 12, 30) {
+      const int e = l - 12, m = e >= 9, j = e - 9 * m;
+      double f;
+      if (j < 3) f = m ? fma(B[3], hd->Y[j], hd->Y[40 + j]) : fma(B[0], hd->Y[j], fma(B[1], hd->Y[4 + j], fma(B[2], hd->Y[8 + j], hd->Y[36 + j])));
+      else f = Yb[j * 2 + m] + Pf[81 + e];
+      hd->Fc[e] = f;
+      c.F[18 * k + e] = f;
+    }
+    Q3_ITEMS(l, 30, 31) { c.Wi[4 * k] = W00; c.Wi[4 * k + 1] = W01; c.Wi[4 * k + 2] = W11; }
+    Q3_ITEMS(l, 31, 32) { c.zk[2 * k] = z0; c.zk[2 * k + 1] = z1; }
     Q3_SYNC();
-    // ---- phase 3: the stage's outputs, then P_k
-    const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
-    const double z0 = W00 * hd->hu[0] + W01 * hd->hu[1], z1 = W01 * hd->hu[0] + W11 * hd->hu[1];
-    Q3_FOR(e, 18) {
-      const int m = e / 9, j = e - 9 * m;
-      c.F[18 * k + e] = j < 3 ? hd->Fs[m * 3 + j] : hd->G[e];
-    }
-    Q3_FOR(e, 2) c.zk[2 * k + e] = e == 0 ? z0 : z1;
+    // ---- phase 3
     if (k > 0) {
-      Q3_FOR(it, 45 + 18 + 3 + 9 + 2) {
-        if (it < 45) {
-          const int ij = hd->tri[it], i = ij >> 4, j = ij & 15;
-          const double f0i = i < 3 ? hd->Fs[i] : hd->G[i], f1i = i < 3 ? hd->Fs[3 + i] : hd->G[9 + i];
-          const double f0j = j < 3 ? hd->Fs[j] : hd->G[j], f1j = j < 3 ? hd->Fs[3 + j] : hd->G[9 + j];
-          const double T = j < 3 ? hd->TA[i * 3 + j] : (i < 3 ? hd->MA[j * 3 + i] : Pxx[i * 9 + j]);
-          const double v = T - (W00 * (f0i * f0j) + W01 * (f0i * f1j + f1i * f0j) + W11 * (f1i * f1j)) + qt3(c, k - 1, i, j);
-          Pxx[i * 9 + j] = v; Pxx[j * 9 + i] = v;
-        } else if (it < 63) {
-          const int e = it - 45, m = e / 9, j = e - 9 * m;
-          const double f0j = j < 3 ? hd->Fs[j] : hd->G[j], f1j = j < 3 ? hd->Fs[3 + j] : hd->G[9 + j];
-          const double fw0 = W00 * f0j + W01 * f1j, fw1 = W01 * f0j + W11 * f1j;
-          Pvx[e] = dR2[m * 2] * fw0 + dR2[m * 2 + 1] * fw1;
-        } else if (it < 66) {
-          const int q = it - 63, m = q == 2 ? 1 : 0, n = q == 0 ? 0 : 1;
-          // (dR2 W dR2)[m][n]
-          const double a0 = dR2[m * 2] * W00 + dR2[m * 2 + 1] * W01, a1 = dR2[m * 2] * W01 + dR2[m * 2 + 1] * W11;
-          const double v = dR2[m * 2 + n] - (a0 * dR2[n] + a1 * dR2[2 + n]);
-          Pvv[m * 2 + n] = v; Pvv[n * 2 + m] = v;
-        } else if (it < 75) {
-          const int j = it - 66;
-          const double f0j = j < 3 ? hd->Fs[j] : hd->G[j], f1j = j < 3 ? hd->Fs[3 + j] : hd->G[9 + j];
-          px[j] = hd->Apx[j] - f0j * z0 - f1j * z1 + c.gx[9 * (k - 1) + j];
-        } else {
-          const int m = it - 75;
-          pv[m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1;
-        }
+      const double* Fc = hd->Fc;
+      Q3_ITEM(e, 45) {
+        const int ij = hd->tri[e], i = ij >> 4, j = ij & 15;
+        const double f0i = Fc[i], f1i = Fc[9 + i], f0j = Fc[j], f1j = Fc[9 + j];
+        const double T = j < 3 ? hd->TA[i * 3 + j] : (i < 3 ? hd->Y[j * 4 + i] : Pf[i * 9 + j]);
+        const double v = T - (W00 * (f0i * f0j) + W01 * (f0i * f1j + f1i * f0j) + W11 * (f1i * f1j)) + qt3(c, k - 1, e);
+        Pf[i * 9 + j] = v; Pf[j * 9 + i] = v;
       }
+      Q3_ITEM(e, 18) {
+        const int m = e >= 9, j = e - 9 * m;
+        const double fw0 = W00 * Fc[j] + W01 * Fc[9 + j], fw1 = W01 * Fc[j] + W11 * Fc[9 + j];
+        Pf[81 + e] = dR2[m * 2] * fw0 + dR2[m * 2 + 1] * fw1;
+      }
+      Q3_ITEM(j, 9) px[j] = (j < 3 ? hd->Apx[j] : hd->pe[j]) - Fc[j] * z0 - Fc[9 + j] * z1 + c.gx[9 * (k - 1) + j];
+      Q3_ITEMS(l, 9, 11) { const int m = l - 9; pv[m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1; }
+      Q3_ITEMS(l, 11, 14) {
+        const int q = l - 11, m = q == 2, n = q != 0;  // (0,0) (0,1) (1,1)
+        const double a0 = dR2[m * 2] * W00 + dR2[m * 2 + 1] * W01, a1 = dR2[m * 2] * W01 + dR2[m * 2 + 1] * W11;
+        const double v = dR2[m * 2 + n] - (a0 * dR2[n] + a1 * dR2[2 + n]);
+        hd->Pvv[m * 2 + n] = v; hd->Pvv[n * 2 + m] = v;
+      }
+      if (defects) Q3_ITEMS(l, 14, 23) hd->dbuf[(k - 1) & 1][l - 14] = defect3(c, k - 1, l - 14);
     }
     Q3_SYNC();
   }
 }
 
-// Backward pass for a new gradient with the factor kept from ric_factor_backward3 (zero defects).
+// Backward pass for a new gradient with the factor kept from ric_factor_backward3 (zero defects).  One phase per stage.
 // ye != nullptr: the costates are written as the multipliers of the dynamics rows (rows of G, LPV_Planner.py:429-475):
 // ye[12 t + j] = -px_t[j], t = N .. 1, and row block 0 from one adjoint step (gq0 = gradient of the cost in x_0).
 Q3D void ric_affine_backward3(const Ctx3& c, double* ye) {
   Hdr3* hd = c.hd;
   const int N = c.N;
   const double* dR2 = hd->dR2;
-  Q3_FOR(e, 9) hd->px[0][e] = c.gx[9 * (N - 1) + e];
-  Q3_FOR(e, 2) hd->pv[0][e] = 0.0;
+  Q3_ITEM(e, 9) hd->px[0][e] = c.gx[9 * (N - 1) + e];
+  Q3_ITEM(e, 2) hd->pv[0][e] = 0.0;
   Q3_SYNC();
   int cur = 0;
 #pragma unroll 1
@@ -652,51 +634,49 @@ Q3D void ric_affine_backward3(const Ctx3& c, double* ye) {
     const double hu1 = c.gu[2 * k + 1] + pvin[1] + B[3] * pin[0];
     const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
     const double z0 = W00 * hu0 + W01 * hu1, z1 = W01 * hu0 + W11 * hu1;
-    Q3_FOR(it, 13) {
-      if (it < 9) {
-        const int j = it;
-        double v;
-        if (j < 3) {
-          double s0 = 0.0, s1 = 0.0;
+    Q3_ITEM(j, 9) {
+      double v = pin[j];
+      if (j < 3) {
+        double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-          for (int l = 0; l < 8; l += 2) { s0 = fma(A[l * 3 + j], pin[l], s0); s1 = fma(A[(l + 1) * 3 + j], pin[l + 1], s1); }
-          v = fma(A[24 + j], pin[8], s0) + s1;
-        } else {
-          v = pin[j];
+        for (int q = 0; q < 8; q += 2) { a0 = fma(A[3 * q + j], pin[q], a0); a1 = fma(A[3 * q + 3 + j], pin[q + 1], a1); }
+        v = fma(A[24 + j], pin[8], a0) + a1;
+      }
+      if (ye) ye[12 * (k + 1) + j] = -pin[j];
+      if (k > 0) hd->px[cur ^ 1][j] = v - Fk[j] * z0 - Fk[9 + j] * z1 + c.gx[9 * (k - 1) + j];
+      else if (ye) {
+        double gq = j == 0 ? hd->q0 : 0.0;
+        for (int q = 0; q < hd->nq; ++q) {
+          const int e = hd->nzl[q], qi = hd->tri[e] >> 4, qj = hd->tri[e] & 15;
+          if (qi == j) gq = fma(hd->Q2u[e], hd->x0[qj], gq);
+          else if (qj == j) gq = fma(hd->Q2u[e], hd->x0[qi], gq);
         }
-        if (ye) ye[12 * (k + 1) + j] = -pin[j];
-        if (k > 0) hd->px[cur ^ 1][j] = v - Fk[j] * z0 - Fk[9 + j] * z1 + c.gx[9 * (k - 1) + j];
-        else if (ye) {
-          double gq = j == 0 ? hd->q0 : 0.0;
-          for (int l = 0; l < 9; ++l) gq = fma(hd->Q2[j * 9 + l], hd->x0[l], gq);
-          ye[j] = -(v + gq);
-        }
-      } else if (it < 11) {
-        const int m = it - 9;
-        hd->pv[cur ^ 1][m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1;
-      } else {
-        c.zk[2 * k + (it - 11)] = it == 11 ? z0 : z1;
+        ye[j] = -(v + gq);
       }
     }
+    Q3_ITEMS(l, 9, 11) { const int m = l - 9; hd->pv[cur ^ 1][m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1; }
+    Q3_ITEMS(l, 11, 12) { c.zk[2 * k] = z0; c.zk[2 * k + 1] = z1; }
     Q3_SYNC();
     cur ^= 1;
   }
 }
 
-// Forward pass: c.du, c.dx (c.dx holds the defects on input), then the slack steps from c.gs.  acc: the sweep's step is
-// ADDED to c.dx / c.du (corrector increment on top of the predictor; no defects) - the slack steps, linear in (dx, gs),
-// are recomputed from the totals.  Ends with a barrier.
-Q3D void ric_forward3(const Ctx3& c, int acc) {
+// Forward pass: c.du, c.dx (over the gradient's storage), then the slack steps (c.dsig over c.gs).  defects: the
+// dynamics defect of the iterate is added stage by stage, so that a full step lands on a dynamics-consistent point.
+// One phase per stage.  Ends with a barrier.
+Q3D void ric_forward3(const Ctx3& c, const int defects) {
   Hdr3* hd = c.hd;
   const double* dR2 = hd->dR2;
+  double* fx = hd->Y;        // the running stage's step (ping-pong 2 x 9, 2 x 2): over the backward sweeps' scratch
+  double* fu = hd->Y + 18;
   int cur = 0;
 #pragma unroll 1
   for (int k = 0; k < c.N; ++k) {
     const double* A = c.Acol + 27 * k;
     const double* B = c.Bcol + 4 * k;
     const double* Fk = c.F + 18 * k;
-    const double* xin = hd->fx[cur];
-    const double* vin = hd->fu[cur];
+    const double* xin = fx + 9 * cur;
+    const double* vin = fu + 2 * cur;
     double du0 = -c.zk[2 * k], du1 = -c.zk[2 * k + 1];
     if (k > 0) {
       double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
@@ -711,22 +691,21 @@ Q3D void ric_forward3(const Ctx3& c, int acc) {
       du0 -= W00 * r0 + W01 * r1;
       du1 -= W01 * r0 + W11 * r1;
     }
-    Q3_FOR(it, 11) {
-      if (it < 9) {
-        double v = (k > 0 ? arow3(A, xin, it) : 0.0) + brow3(B, du0, du1, it);
-        if (!acc) v += c.dx[9 * k + it];
-        hd->fx[cur ^ 1][it] = v;
-        c.dx[9 * k + it] = acc ? c.dx[9 * k + it] + v : v;
-      } else {
-        const double v = it == 9 ? du0 : du1;
-        hd->fu[cur ^ 1][it - 9] = v;
-        c.du[2 * k + (it - 9)] = acc ? c.du[2 * k + (it - 9)] + v : v;
-      }
+    Q3_ITEM(j, 9) {
+      double v = (k > 0 ? arow3(A, xin, j) : 0.0) + brow3(B, du0, du1, j);
+      if (defects) v += defect3(c, k, j);
+      fx[9 * (cur ^ 1) + j] = v;
+      c.dx[9 * k + j] = v;
+    }
+    Q3_ITEMS(l, 9, 11) {
+      const double v = l == 9 ? du0 : du1;
+      fu[2 * (cur ^ 1) + (l - 9)] = v;
+      c.du[2 * k + (l - 9)] = v;
     }
     Q3_SYNC();
     cur ^= 1;
   }
-  // slack steps: dsig = -Si (bh' do + gs)
+  // slack steps: dsig = -Si (bh' do + gs), in place over gs
   Q3_FOR(t, c.N) {
     const double* si = c.Si + 6 * t;
     const double* bh = c.bh + 4 * t;
@@ -742,20 +721,22 @@ Q3D void ric_forward3(const Ctx3& c, int acc) {
 }
 
 // One instantiation each of the two solves (they are called from the active-set rounds and from the interior point).
-// c.D must be final and barrier-visible.  mode / smu: see assemble_gradient3.
-Q3N void factor_solve3(int mode) {
+// c.D must be final and barrier-visible.  mode / smu: see row_w3.  defects: the iterate is not dynamics-consistent (the
+// bounded starting point): the solve removes the defects, a full step lands on a consistent point.  Every later step is
+// a combination of consistent directions, so the iterate stays consistent to rounding and the flag stays off.
+Q3N void factor_solve3(int mode, int defects) {
   Q3_CTX(c);
   stage_weights3(c);
-  assemble_gradient3(c, mode, 0.0, 1);
-  ric_factor_backward3(c);
-  ric_forward3(c, 0);
+  assemble_gradient3(c, mode, 0.0);
+  ric_factor_backward3(c, defects);
+  ric_forward3(c, defects);
   if (Q3_LANE == 0) { ++c.hd->n_fact; ++c.hd->n_solve; }
 }
 Q3N void affine_solve3(int mode, double smu) {
   Q3_CTX(c);
-  assemble_gradient3(c, mode, smu, 0);
+  assemble_gradient3(c, mode, smu);
   ric_affine_backward3(c, nullptr);
-  ric_forward3(c, mode == G3_COR);
+  ric_forward3(c, 0);
   if (Q3_LANE == 0) ++c.hd->n_solve;
 }
 

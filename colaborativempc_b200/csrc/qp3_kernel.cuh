@@ -25,8 +25,13 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
       for (int i = 0; i < 4; ++i) { hd->R2[i] = 2.0 * P.R[i]; hd->dR2[i] = 2.0 * P.dR[i]; }
       for (int i = 0; i < 9; ++i) hd->Qs2[i] = 2.0 * P.Qs[i];
       hd->uold[0] = io.uold[(size_t)b * 2]; hd->uold[1] = io.uold[(size_t)b * 2 + 1];
+      int nq = 0, e = 0;
+      for (int i = 0; i < 9; ++i) for (int j = i; j < 9; ++j, ++e) {
+        hd->Q2u[e] = 2.0 * P.Qf[i * 9 + j];
+        if (P.Qf[i * 9 + j] != 0.0) hd->nzl[nq++] = (unsigned char)e;
+      }
+      hd->nq = nq;
     }
-    Q3_FOR(i, 81) hd->Q2[i] = 2.0 * P.Qf[i];
     Q3_FOR(i, 9) hd->x0[i] = io.x0[(size_t)b * NSTATE + i];
     Q3_SYNC();
   }
@@ -64,7 +69,22 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
   } else {
     // ---------------- solve ----------------
     double* park = io.gws + (size_t)b * io.gws_stride;
-    status = solve_qp3(c, park);
+    // what the previous call of this batch size spent on this QP index (valid exactly when the launch order is)
+    const int hard_hint = io.order && io.cost && ((io.cost[b] >> 21) & 1);
+    status = solve_qp3(c, park, io.warm ? io.warm + (size_t)b * c.RT : nullptr, hard_hint);
+    if (io.warm) {  // the certified working set is the next call's first guess (nothing to offer if not certified)
+      unsigned char* w = io.warm + (size_t)b * c.RT;
+      const int ok = status == DMPC_SOLVED;
+      Q3_FOR(j, c.RT) {
+        int src = j;
+        if (io.warm_shift) {  // stage k of the next step is stage k+1 of this one; the last stage repeats
+          const int per = j < c.Rs ? c.rst : 4, base = j < c.Rs ? 0 : c.Rs;
+          const int kk = (j - base) / per;
+          if (kk < N - 1) src = j + per;
+        }
+        w[j] = ok ? c.act[src] : 0;
+      }
+    }
 
     // ---------------- outputs (LPV_Planner.py:162-180 layout of res.x) ----------------
     if (io.z) {
@@ -87,10 +107,9 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
       Q3_FOR(t, N + 1) {
         const double* x = t == 0 ? hd->x0 : c.x + 9 * (t - 1);
         double s = 0.0;
-        for (int i = 0; i < 9; ++i) {
-          double a = 0.0;
-          for (int l = 0; l < 9; ++l) a = fma(hd->Q2[i * 9 + l], x[l], a);
-          s = fma(0.5 * a, x[i], s);
+        for (int q = 0; q < hd->nq; ++q) {
+          const int e = hd->nzl[q], i = hd->tri[e] >> 4, j = hd->tri[e] & 15;
+          s = fma((i == j ? 0.5 : 1.0) * hd->Q2u[e] * x[i], x[j], s);
         }
         s = fma(hd->q0, x[0], s);
         if (t >= 1) {
@@ -112,7 +131,7 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
     // solution: one affine backward pass on the Lagrangian gradient with the factor of the last solve
     if (io.y_eq) {
       double* ye = io.y_eq + (size_t)b * (14 * N + 12);
-      assemble_gradient3(c, G3_LAG, 0.0, 0);
+      assemble_gradient3(c, G3_LAG, 0.0);
       ric_affine_backward3(c, ye);
       Q3_FOR(t, N + 1) { ye[12 * t + 9] = 0.0; ye[12 * t + 10] = 0.0; ye[12 * t + 11] = 0.0; }
       Q3_FOR(k, N) {
@@ -126,7 +145,7 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
     if (Q3_LANE == 0) {
       if (io.iters) io.iters[b] = hd->n_ipm;
       if (io.pivots) io.pivots[b] = hd->n_rounds;
-      if (io.cost) io.cost[b] = 3 * hd->n_fact + hd->n_solve;
+      if (io.cost) io.cost[b] = (3 * hd->n_fact + hd->n_solve) | (1 << 20) | (hd->n_ipm > 0 ? 1 << 21 : 0);  // bit 20: stage-wise cost scale, bit 21: interior point used
     }
   }
   if (Q3_LANE == 0 && io.status) io.status[b] = status;
@@ -157,8 +176,8 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
 
 #ifndef QP3_HOST
 __global__ void __launch_bounds__(QP3_THREADS) lpv_qp_stage_kernel(const __grid_constant__ DevParams P, const BatchPtrs io) {
-  const int b = blockIdx.x;
-  if (b >= io.B) return;
+  if ((int)blockIdx.x >= io.B) return;
+  const int b = io.order ? io.order[blockIdx.x] : blockIdx.x;  // most expensive QPs of the previous call first
   if (io.only_status && io.status[b] != io.only_status) return;
   solve_one_qp3(P, io, b);
 }

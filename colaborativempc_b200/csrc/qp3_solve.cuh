@@ -14,9 +14,10 @@
 // loose thresholds that decide "the guess is clearly wrong, do not spend refinement passes on it"
 #define Q3_LOOSE 1e-6
 
-// One active-set round on c.act.  Returns 1 certified, 0 guess updated (c.act), 2 numerical failure (non-finite).
+// One active-set round on c.act.  first: the iterate is the bounded starting point, not yet dynamics-consistent.
+// Returns 1 certified, 0 guess updated (c.act), 2 numerical failure (non-finite).
 // On exit c.x, c.u, c.sig, c.lam, c.res belong to the guess that was solved.
-Q3N int polish_round3() {
+Q3N int polish_round3(int first) {
   Q3_CTX(c);
   Hdr3* hd = c.hd;
   // Penalty of the rows in the guess.  A soft row (one with a slack) is only ever as stiff as its slack weight: after
@@ -33,7 +34,7 @@ Q3N int polish_round3() {
   }
   Q3_SYNC();
   eval_residuals3(c);
-  factor_solve3(G3_ALM);
+  factor_solve3(G3_ALM, first);
   primal_step3(c, 1.0);
   int pass = 0;
 #pragma unroll 1
@@ -100,19 +101,22 @@ Q3D unsigned long long act_hash3(const Ctx3& c) {
 }
 
 // Up to `rounds` rounds; 1 certified, 0 not (cycle or round cap), 2 numerical failure.
-Q3N int pdas3(int rounds) {
+Q3N int pdas3(int rounds, int first) {
   Q3_CTX(c);
   int nh = 0;
 #pragma unroll 1
   for (int r = 0; r < rounds; ++r) {
-    const int st = polish_round3();
+    const int st = polish_round3(first && r == 0);
     if (Q3_LANE == 0) ++c.hd->n_rounds;
+#ifdef QP3_TRACE2
+    { int na = 0; for (int j = 0; j < c.RT; ++j) na += c.act[j]; printf("R %d %d %d\n", r, st, na); }
+#endif
     if (st) return st;
     const unsigned long long h = act_hash3(c);
     int cyc = 0;
-    for (int i = 0; i < nh && i < 16; ++i) cyc |= (c.hd->hist[i] == h);
+    for (int i = 0; i < nh && i < 8; ++i) cyc |= (c.hd->hist[i] == h);
     Q3_SYNC();
-    if (Q3_LANE == 0 && nh < 16) c.hd->hist[nh] = h;
+    if (Q3_LANE == 0) c.hd->hist[nh & 7] = h;
     ++nh;
     Q3_SYNC();
     if (cyc) return 0;
@@ -163,11 +167,12 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     Q3_FOR(j, 3 * c.N) c.sig[j] = 0.0;
     Q3_SYNC();
     eval_residuals3(c);
-    factor_solve3(G3_ALM);
+    factor_solve3(G3_ALM, 1);
     primal_step3(c, 1.0);
     eval_residuals3(c);
     const double qsm = 0.5 * fmax(hd->Qs2[0], fmax(hd->Qs2[4], hd->Qs2[8]));
-    const double lam_scale = fmax(1.0, 1e-3 * qsm);
+    // multipliers of violated soft rows end near 2 Qs sigma: start the duals at 1e-4 max(Qs) rather than O(1)
+    const double lam_scale = fmax(1.0, 1e-4 * qsm);
     double mt = 1e300, ml = 1e300;
     Q3_FOR(j, c.RT)
       if (row_ok3(c, j)) { mt = fmin(mt, -c.res[j]); ml = fmin(ml, c.res[j]); }
@@ -196,7 +201,7 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     double v_obj = 0.0;
     Q3_FOR(k, c.N) {  // scale of the objective (the exact value is computed by the epilogue)
       const double* xk = c.x + 9 * k;
-      for (int i = 0; i < 9; ++i) v_obj += xk[i] * (0.5 * hd->Q2[i * 9 + i] * xk[i]);
+      for (int q = 0; q < hd->nq; ++q) { const int e = hd->nzl[q], i = hd->tri[e] >> 4; if (i == (hd->tri[e] & 15)) v_obj += xk[i] * (0.5 * hd->Q2u[e] * xk[i]); }
       v_obj += hd->q0 * xk[0];
     }
     const double mu = q3_wsum(v_mu) / m;
@@ -210,7 +215,7 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     // ---- predictor (factorisation for D = lam / t)
     Q3_FOR(j, c.RT) c.D[j] = row_ok3(c, j) ? c.lam[j] / c.tt[j] : 0.0;
     Q3_SYNC();
-    factor_solve3(G3_AFF);
+    factor_solve3(G3_AFF, 0);
     Q3_FOR(j, c.RT) {
       if (!row_ok3(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
       const double dt = -(c.res[j] + c.tt[j]) - row_val3(c, j, c.dx, c.dsig, c.du);
@@ -224,8 +229,7 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
       if (row_ok3(c, j)) v_aff = fma(c.lam[j] + aa * c.dlam[j], c.tt[j] + aa * c.dtt[j], v_aff);
     const double mu_aff = q3_wsum(v_aff) / m;
     const double sr = mu_aff / mu, smu = sr * sr * sr * mu;
-    // ---- corrector increment: same factor, right-hand side (smu - dt_aff dlam_aff) / t on the rows only; by linearity
-    // its step is added to the predictor's in place (dx, du, and the slack steps from the summed slack gradient)
+    // ---- corrector: same factor, full right-hand side with the second-order term (smu - dt_aff dlam_aff) / t
     affine_solve3(G3_COR, smu);
     Q3_FOR(j, c.RT) {
       if (!row_ok3(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
@@ -236,6 +240,9 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     }
     Q3_SYNC();
     const double al = fmin(1.0, 0.99 * fmin(step_to_boundary3(c, c.tt, c.dtt), step_to_boundary3(c, c.lam, c.dlam)));
+#ifdef QP3_TRACE3
+    printf("  ipm it %d mu %.3e rp %.3e lin %.2e aa %.3f sig %.3f al %.4f lmax %.2e\n", it, mu, rp, lin, aa, sr*sr*sr, al, lmax);
+#endif
     primal_step3(c, al);
     Q3_FOR(j, c.RT) {
       c.tt[j] = fma(al, c.dtt[j], c.tt[j]);
@@ -248,20 +255,24 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
 }
 
 // Full solve.  Returns dmpc_status; the header counts the work done.  `park`: the QP's global scratch slice.
-Q3D int solve_qp3(const Ctx3& c, double* park) {
+Q3D int solve_qp3(const Ctx3& c, double* park, const unsigned char* warm, const int hard_hint) {
   Hdr3* hd = c.hd;
-  // first guess: the empty working set, from a bounded (not dynamics-consistent) point; the first solve removes the
-  // dynamics defects, so the round returns the unconstrained optimum and adds the rows it violates
-  Q3_FOR(j, c.RT) c.act[j] = 0;
+  // first guess: the working set the previous solve of this QP certified (consecutive MPC steps are alike: usually it IS
+  // the answer and one round certifies it), else the empty set; the rounds correct a wrong guess either way.  The
+  // iterate starts from a bounded (not dynamics-consistent) point; the first solve removes the dynamics defects.
+  Q3_FOR(j, c.RT) c.act[j] = warm ? (warm[j] != 0 && row_ok3(c, j)) : 0;
   Q3_FOR(j, 9 * c.N) c.x[j] = hd->x0[j % 9];
   Q3_FOR(j, 2 * c.N) c.u[j] = 0.0;
   Q3_FOR(j, 3 * c.N) c.sig[j] = 0.0;
   Q3_SYNC();
   {
-    const int st = pdas3(3 * hd->pdas_first);  // same budget as the condensed engine's free rounds
+    // budget: 3 pdas_first rounds (as the condensed engine's free rounds); a QP that ended in the interior point last
+    // time gets two rounds on its previous working set and then goes there directly
+    const int st = pdas3(hard_hint ? 2 : 3 * hd->pdas_first, 1);
     if (st == 1) return DMPC_SOLVED;
   }
-  double mu_tol = hd->ipm_mu0, mu_ok = 0.0;
+  // the first phase goes two decades below the option: the iterations there cost a tenth of a polish attempt on a wrong guess
+  double mu_tol = 1e-2 * hd->ipm_mu0, mu_ok = 0.0;
 #pragma unroll 1
   while (mu_tol > 1e-13) {
     const int rc = ipm3(mu_tol, mu_ok > 0.0, park);
@@ -272,7 +283,7 @@ Q3D int solve_qp3(const Ctx3& c, double* park) {
     if (rc == 0) { mu_ok = mu_tol; ipm_park3(c, park, 1); }
     Q3_FOR(j, c.RT) c.act[j] = row_ok3(c, j) && (c.lam[j] > c.tt[j]);
     Q3_SYNC();
-    if (pdas3(hd->pdas_after) == 1) return DMPC_SOLVED;
+    if (pdas3(hd->pdas_after, 0) == 1) return DMPC_SOLVED;
     if (rc == 2) break;  // iteration cap: a tighter target from the same start would hit it again
     mu_tol *= 1e-2;
   }

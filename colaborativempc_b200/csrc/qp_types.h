@@ -51,6 +51,10 @@ struct BatchPtrs {
   // what the condensed engine could not factorise.  The nx_* / hold pointers (all or none) make the epilogue do the
   // caller's bookkeeping of planner/scripts/LPV_HP_N_main.py:106,113-117 itself (dmpc_shift_io).
   int only_status;
+  // warm start: warm[b][row] (bytes, in/out) = the working set the previous call certified for QP b; warm_shift = 1 stores
+  // it moved one stage towards the present (the next closed-loop step sees stage k+1 as its stage k)
+  unsigned char* warm;
+  int warm_shift;
   double *nx_x0, *nx_xprev, *nx_uprev, *nx_uold, *nx_xy;
   int* hold;
 };

@@ -70,6 +70,11 @@ typedef struct dmpc_options {
                              (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory) the kernel reads and writes it
                              in place over PCIe instead of staging copies; pageable buffers always take the staged
                              path.  Results are identical.  0 = always stage                                         */
+  int32_t warm_start;     /* stage-wise engine: first working-set guess of a QP = the set the previous call of the same batch
+                             size certified for that QP index (handle-owned, starts empty).  1 = as certified, 2 = moved one
+                             stage towards the present (consecutive closed-loop steps: dmpc_solve_shift_batch callers),
+                             0 = always start from the empty set.  Any guess leads to the same certified optimum (agreement
+                             to the certificate tolerance, not bit for bit); a good one saves the active-set rounds.       */
 } dmpc_options;
 
 /* Per-QP status values mirror OSQP's status_val so `feasible` is derived as LPV_Planner.py:246-248. */

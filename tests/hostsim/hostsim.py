@@ -43,11 +43,13 @@ def default_options():
     o = DmpcOptions()
     o.polish_delta, o.cert_tol, o.ipm_mu0 = 1e-9, 1e-9, 1e-6
     o.polish_refine, o.pdas_first, o.pdas_after, o.ipm_max_iter = 4, 4, 2, 60
-    o.engine, o.order_hint, o.host_direct = 3, 0, 0
+    o.engine, o.order_hint, o.host_direct, o.warm_start = 3, 0, 0, 0
     return o
 
 
-def solve_batch(params, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, options=None, shift=False):
+def solve_batch(params, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, options=None, shift=False, warm=None,
+                warm_shift=0):
+    """warm: uint8 [B, (8+nn)N] working sets, read as first guesses and overwritten with the certified ones."""
     N, nn = params.N, params.nn
     f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
     x0, xprev, uprev, uold, nbr_xy, pose = f(x0), f(xprev), f(uprev), f(uold), f(nbr_xy), f(pose)
@@ -75,8 +77,11 @@ def solve_batch(params, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, op
             setattr(sh, k, p(a))
         out["next"] = nx
     o = options or default_options()
+    if warm is not None:
+        assert warm.dtype == np.uint8 and warm.flags.c_contiguous and warm.shape == (B, mi)
     rc = lib().qp3_host_solve_batch(C.byref(params), C.byref(o), C.byref(io), C.byref(sh) if sh is not None else None,
-                                    counters.ctypes.data_as(C.c_void_p))
+                                    counters.ctypes.data_as(C.c_void_p), None if warm is None else warm.ctypes.data_as(C.c_void_p),
+                                    C.c_int(int(warm_shift)))
     assert rc == 0
     out["counters"] = counters
     return out

@@ -19,7 +19,7 @@ extern "C" int qp3_host_workspace_bytes(int N, int nn) {
 
 // counters [B,4]: factorisations, solves, active-set rounds, interior-point iterations
 extern "C" int qp3_host_solve_batch(const dmpc_params* p, const dmpc_options* opt, const dmpc_batch_io* io,
-                                    const dmpc_shift_io* sh, int* counters) {
+                                    const dmpc_shift_io* sh, int* counters, unsigned char* warm, int warm_shift) {
   DevParams P;
   memset(&P, 0, sizeof(P));
   fill_dev_params(p, opt, P);
@@ -31,6 +31,7 @@ extern "C" int qp3_host_solve_batch(const dmpc_params* p, const dmpc_options* op
   bp.z = io->z; bp.planes = io->planes; bp.y_ineq = io->y_ineq; bp.y_eq = io->y_eq; bp.obj = io->obj;
   bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
   if (sh) { bp.nx_x0 = sh->x0; bp.nx_xprev = sh->xprev; bp.nx_uprev = sh->uprev; bp.nx_uold = sh->uold; bp.nx_xy = sh->xy_send; bp.hold = sh->hold; }
+  bp.warm = warm; bp.warm_shift = warm_shift;
   const size_t park = stage_park_doubles(P.N, P.nn);
   std::vector<double> gws((size_t)io->B * park);
   bp.gws = gws.data(); bp.gws_stride = (long long)park;

@@ -64,11 +64,11 @@ def _kkt_certificate(cfg, track, ins, out, b, N, nn):
     assert abs(0.5 * z @ Pm @ z + q @ z - out["obj"][b]) < 1e-8 * (1 + abs(out["obj"][b]))
 
 
-@pytest.mark.parametrize("engine", [2, 1])
+@pytest.mark.parametrize("engine", [3, 2])
 @pytest.mark.parametrize("it", [0, 3])
 def test_golden_platoon(built, cfg, track, it, engine):
     """Committed oracle solutions of 16 three-agent platoons (first call: N+1 history rows; later call: N rows),
-    on the fast (shared-memory packed) and on the generic engine."""
+    on the stage-wise (Riccati, engine 3) and on the condensed (engine 2) engine."""
     fx = golden("platoon_N20.npz")
     eng = _engine(cfg, track, options={"engine": engine})
     ins = {k: fx["it%d_%s" % (it, k)] for k in INPUT_KEYS}
@@ -100,26 +100,23 @@ def test_reference_startup_case(built, cfg, track):
     _compare(out, o["z"], o["y"], o["obj"], o["planes"], eng.m_in)
 
 
-def test_low_speed_qp_is_not_reported_infeasible(built, cfg, track):
-    """KNOWN GAP, kept as a regression fixture: a QP of the 16-agent closed loop (scenario 231, agent 3, second DMPC
-    iteration; inputs captured on the GPU by scripts/gpu_find_bad.py, solution = the oracle's certified optimum).  The
-    vehicle crawls (vx 0.57 -> 0.22 over the horizon) where the forward-Euler lateral dynamics of _EstimateABC are
-    unstable (|1 - dt (Cf+Cr)/(m vx)| up to 7): the condensed prediction matrices grow to ~1e11 and the FP64
-    factorisation of the condensed H breaks down in BOTH engines, while the oracle's uncondensed sparse solve is fine.
-    The QP is feasible, so the path must not certify infeasibility (-3): it reports DMPC_UNSOLVED (-10).  When a
-    stage-wise (Riccati) factorisation replaces condensation for such QPs this test starts demanding full parity."""
+@pytest.mark.parametrize("engine", [3, 2])
+def test_low_speed_qp_is_solved(built, cfg, track, engine):
+    """A QP of the 16-agent closed loop (scenario 231, agent 3, second DMPC iteration; inputs captured on the GPU in round
+    1, solution = the oracle's certified optimum).  The vehicle crawls (vx 0.57 -> 0.22 over the horizon) where the
+    forward-Euler lateral dynamics of _EstimateABC are unstable (|1 - dt (Cf+Cr)/(m vx)| up to 7): the condensed
+    prediction matrices grow to ~1e11 and the condensed Hessian cannot be factorised in FP64.  The reference hands the
+    UNCONDENSED QP to OSQP (LPV_Planner.py:222-239) and solves it; so must this path: the stage-wise engine directly, the
+    condensed engine by re-solving stage-wise what it reports as DMPC_UNSOLVED, inside the same call."""
     g = golden("closed_loop_ipm_start_qp.npz")
-    for engine in (2, 1):
-        eng = _engine(cfg, track, options={"engine": engine})
-        out = eng.solve_batch_host(**{k: g["in_" + k] for k in INPUT_KEYS})
-        assert out["status"][0] in (1, 2, -10), out["status"]
-        if out["status"][0] == 1:
-            _compare(out, g["out_z"], g["out_y"], g["out_obj"], g["out_planes"], eng.m_in)
+    eng = _engine(cfg, track, options={"engine": engine})
+    out = eng.solve_batch_host(**{k: g["in_" + k] for k in INPUT_KEYS})
+    _compare(out, g["out_z"], g["out_y"], g["out_obj"], g["out_planes"], eng.m_in)
 
 
 def test_recorded_reference_run_horizon_125(built, cfg, track):
     """The reference's recorded experiment (LPV3r_agent_laptop, N=125): its first DMPC iteration from the reference's
-    cold start through the CUDA path (generic engine, global-memory workspace).  Parity with the oracle's certified
+    cold start through the CUDA path (stage-wise engine, 125 stages in shared memory).  Parity with the oracle's certified
     optimum at 1e-6; against the recorded uPred - an un-polished OSQP iterate at eps 1e-3, see
     test_restated_osqp_reproduces_the_reference_recorded_run - the optimum sits within 0.1 (9.1e-2 / 5.9e-2 / 4.2e-2,
     SURVEY 8c), and the recorded point's objective is not better than ours once its constraint violation is paid for."""
@@ -133,48 +130,45 @@ def test_recorded_reference_run_horizon_125(built, cfg, track):
     sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), np.stack([x[0] for x in xs])[None], np.stack(xs)[None],
                 np.stack(us)[None], idx, cnt, 1, Nh, record=log)
     ins, out = log[0]
-    assert np.all(np.isin(out["status"], (1, 2)))
     o = _oracle(cfg, track, ins, N=Nh, nn=2, nthreads=3)
     assert np.all(o["status"] == 1)
+    _compare(out, o["z"], o["y"], o["obj"], o["planes"], eng.m_in)
     u0 = 12 * (Nh + 1)
     for i in range(3):
-        tol = TOL if out["status"][i] == 1 else 1e-5
-        assert rel_err(out["z"][i:i + 1], o["z"][i:i + 1]).max() < tol
-        assert abs(out["obj"][i] - o["obj"][i]) < TOL * abs(o["obj"][i])
         u = out["z"][i, u0:u0 + 2 * Nh].reshape(Nh, 2)
         assert np.abs(u - rec["u_it0_agent%d" % i]).max() < 0.1
-        if out["status"][i] == 1:
-            _kkt_certificate(cfg, track, ins, out, i, Nh, 2)
+        _kkt_certificate(cfg, track, ins, out, i, Nh, 2)
 
 
-@pytest.mark.parametrize("Nh,nn,topo,S,A", [(10, 2, "full", 8, 3), (20, 2, "chain", 4, 6), (20, 5, "full", 4, 6),
-                                            (50, 2, "full", 4, 3), (20, 0, "full", 8, 1)])
-def test_closed_loop_vs_oracle(built, cfg, track, Nh, nn, topo, S, A):
-    """4 DMPC iterations driven by the CUDA path; every iteration's batch is re-solved by the oracle."""
+@pytest.mark.parametrize("Nh,nn,topo,S,A,iters", [(10, 2, "full", 8, 3, 4), (20, 2, "chain", 4, 6, 4), (20, 5, "full", 4, 6, 4),
+                                                  (50, 2, "full", 4, 3, 4), (20, 0, "full", 8, 1, 4), (100, 2, "full", 2, 3, 3),
+                                                  (20, 15, "full", 2, 16, 3)])
+def test_closed_loop_vs_oracle(built, cfg, track, Nh, nn, topo, S, A, iters):
+    """DMPC iterations driven by the CUDA path; every iteration's batch is re-solved by the oracle.  Every QP the oracle's
+    exact mode certifies must come back certified (status 1) and is compared at 1e-6 with the same active set; a QP the
+    oracle's exact mode does not certify (its sparse interior point gives up on some long-horizon QPs with near-dependent
+    active rows) may come back 1 or 2 and is held to the independent KKT certificate on the reference-assembled matrices."""
     from colaborativempc_b200 import scenarios as sc
     eng = _engine(cfg, track, N=Nh, nn=nn, max_batch=S * A)
     x0, xprev, uprev = sc.platoon_scenarios(S, A, Nh, cfg["dt"], track, seed0=100)
     idx, cnt = sc.topology(A, topo, nn=nn)
     rec = []
-    sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, 4, Nh, record=rec)
-    assert len(rec) == 4
+    sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, iters, Nh, record=rec)
+    assert len(rec) == iters
     n_cmp = 0
     for ins, out in rec:
-        # status 2 (OSQP's "solved inaccurate"): no active set certified -- degenerate rows on long horizons (vx >= 0 rows
-        # next to saturated braking are linearly dependent); the interior-point iterate is returned instead
-        assert np.all(np.isin(out["status"], (1, 2))) and (out["status"] == 1).mean() >= 0.9
         o = _oracle(cfg, track, ins, N=Nh, nn=nn)
         ok = o["status"] == 1
-        assert ok.mean() >= 0.75
-        both = ok & (out["status"] == 1)
-        _compare({k: v[both] for k, v in out.items()}, o["z"][both], o["y"][both], o["obj"][both], o["planes"][both], eng.m_in)
-        n_cmp += int(both.sum())
-        loose = ok & (out["status"] == 2)
-        if loose.any():
-            assert rel_err(out["z"][loose], o["z"][loose]).max() < 1e-5
-            assert rel_err(out["obj"][loose, None], o["obj"][loose, None]).max() < 1e-6
-        if nn > 0 and np.all(ins["nbr_count"] == nn):
-            for b in np.flatnonzero(~ok & (out["status"] == 1)):
+        assert ok.mean() >= 0.6
+        # every QP the oracle's exact mode certifies must come back certified; status 2 ("solved inaccurate": the
+        # interior-point iterate, no working set certified - near-dependent active rows on long horizons) is accepted
+        # only where the oracle's exact mode does not certify either
+        assert np.all(out["status"][ok] == 1), np.unique(out["status"][ok], return_counts=True)
+        assert np.all(np.isin(out["status"][~ok], (1, 2)))
+        _compare({k: v[ok] for k, v in out.items()}, o["z"][ok], o["y"][ok], o["obj"][ok], o["planes"][ok], eng.m_in)
+        n_cmp += int(ok.sum())
+        if nn > 0 and np.all(ins["nbr_count"] == nn):  # independent KKT check on the reference-assembled matrices
+            for b in np.flatnonzero(~ok):
                 _kkt_certificate(cfg, track, ins, out, b, Nh, nn)
     assert n_cmp > 0
 
@@ -182,7 +176,7 @@ def test_closed_loop_vs_oracle(built, cfg, track, Nh, nn, topo, S, A):
 def test_device_and_host_entry_points_agree(built, cfg, track):
     import torch
     fx = golden("platoon_N20.npz")
-    eng = _engine(cfg, track)
+    eng = _engine(cfg, track, options={"warm_start": 0, "order_hint": 0})  # bit-for-bit: every call starts from the empty guess
     ins = {k: fx["it3_%s" % k] for k in INPUT_KEYS}
     h = eng.solve_batch_host(**ins)
     dev = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in ins.items()}
@@ -190,8 +184,7 @@ def test_device_and_host_entry_points_agree(built, cfg, track):
     torch.cuda.synchronize()
     for k in ("z", "y_ineq", "y_eq", "obj", "status", "planes"):
         assert np.array_equal(d[k].cpu().numpy(), h[k]), k
-    # fast engine: solve + launch-order kernel; from the second call of a batch size on, the solve is a split launch
-    assert eng.launches == (5 if eng.fast else 2)
+    assert eng.launches == 2  # stage-wise engine: one launch per call, the whole of PlannerLPV.solve
 
 
 def test_page_locked_host_buffers_are_used_in_place(built, cfg, track):
@@ -201,8 +194,8 @@ def test_page_locked_host_buffers_are_used_in_place(built, cfg, track):
     import torch
     fx = golden("platoon_N20.npz")
     ins = {k: fx["it3_%s" % k] for k in INPUT_KEYS}
-    staged = _engine(cfg, track, options={"host_direct": 0}).solve_batch_host(**ins)
-    eng = _engine(cfg, track)
+    staged = _engine(cfg, track, options={"host_direct": 0, "warm_start": 0}).solve_batch_host(**ins)
+    eng = _engine(cfg, track, options={"warm_start": 0})
     B = ins["x0"].shape[0]
 
     def pinned(a, pad=0):  # a copy of `a` living `pad` elements into a page-locked allocation
@@ -220,7 +213,7 @@ def test_page_locked_host_buffers_are_used_in_place(built, cfg, track):
 
 
 def test_cost_ordered_launch_changes_nothing(built, cfg, track):
-    """order_hint only permutes which CTA solves which QP (most expensive of the previous call first): outputs are
+    """Condensed engine (engine 2).  order_hint only permutes which CTA solves which QP (most expensive of the previous call first): outputs are
     bit-identical with the hint off, on the first call (identity order) and on later calls (sorted order), also when
     the batch size changes between calls."""
     from colaborativempc_b200 import scenarios as sc
@@ -228,9 +221,9 @@ def test_cost_ordered_launch_changes_nothing(built, cfg, track):
     x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=7)
     idx, cnt = sc.topology(A, "chain", nn=2)
     rec = []
-    ref = _engine(cfg, track, max_batch=S * A, options={"order_hint": 0})
+    ref = _engine(cfg, track, max_batch=S * A, options={"order_hint": 0, "engine": 2})
     sc.run_dmpc(lambda **kw: ref.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, 3, N, record=rec)
-    eng = _engine(cfg, track, max_batch=S * A)
+    eng = _engine(cfg, track, max_batch=S * A, options={"engine": 2})
     keys = ("z", "y_ineq", "y_eq", "obj", "status", "planes", "iters", "pivots")
     for rep in range(2):
         for ins, out in rec:
@@ -241,7 +234,9 @@ def test_cost_ordered_launch_changes_nothing(built, cfg, track):
     got = eng.solve_batch_host(**half)
     for k in keys:
         assert np.array_equal(got[k], rec[1][1][k][: S * A // 2], equal_nan=k not in ("status", "iters", "pivots")), k
-    assert ref.launches == 3 and eng.launches == 19  # hint on: 2 launches on a first call of a batch size, then 3
+    # condensed engine: solve (split in two from the second call of a batch size on) + launch-order kernel + the
+    # stage-wise pass over what it could not factorise
+    assert ref.launches == 6 and eng.launches == 26
 
 
 def test_drop_in_planner_matches_reference_call_surface(built, cfg, track):
@@ -301,7 +296,7 @@ def test_full_size_batch_properties(built, cfg, track):
     import torch
     from colaborativempc_b200 import scenarios as sc
     S, A = 64, 3
-    eng = _engine(cfg, track, max_batch=4096)
+    eng = _engine(cfg, track, max_batch=4096, options={"warm_start": 0})  # bitwise properties: no carried guesses
     x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=1000)
     idx, cnt = sc.topology(A, "full")
     st = sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, 3, N)
@@ -321,6 +316,41 @@ def test_full_size_batch_properties(built, cfg, track):
     u = out["z"][:, u0:u0 + 2 * N].reshape(-1, N, 2)
     assert u[:, :, 0].max() <= 0.3 + 1e-9 and u[:, :, 0].min() >= -0.3 - 1e-9
     assert u[:, :, 1].max() <= 5.0 + 1e-9 and u[:, :, 1].min() >= -10.0 - 1e-9
+
+
+def test_warm_start_and_launch_order_change_the_route_not_the_optimum(built, cfg, track):
+    """dmpc_options.warm_start / order_hint: the previous call's certified working sets are the first guesses and its costs
+    the launch order.  Replaying a batch then certifies every QP in ONE round without the interior point; a permuted and a
+    perturbed batch (stale guesses) still certify; all agree with the cold solve to the certificate tolerance."""
+    from colaborativempc_b200 import scenarios as sc
+    S, A = 128, 3
+    cold = _engine(cfg, track, max_batch=S * A, options={"warm_start": 0, "order_hint": 0})
+    x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=2000)
+    idx, cnt = sc.topology(A, "full")
+    st = sc.run_dmpc(lambda **kw: cold.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, 3, N)
+    ins = {k: st[k] for k in INPUT_KEYS}
+    ref = cold.solve_batch_host(**ins)
+    assert np.all(ref["status"] == 1)
+    eng = _engine(cfg, track, max_batch=S * A)
+    first = eng.solve_batch_host(**ins)
+    for k in ("z", "y_ineq", "y_eq", "obj", "status"):
+        assert np.array_equal(first[k], ref[k]), k      # first call of a batch size: empty guesses, identity order
+    again = eng.solve_batch_host(**ins)
+    assert np.all(again["status"] == 1) and np.all(again["pivots"] == 1) and np.all(again["iters"] == 0)
+    assert ref["pivots"].mean() > 2.0
+    perm = np.random.default_rng(1).permutation(S * A)
+    stale = eng.solve_batch_host(**{k: v[perm] for k, v in ins.items()})   # every QP gets another QP's working set
+    moved = dict(ins)
+    moved["x0"] = ins["x0"] + np.random.default_rng(2).normal(scale=1e-3, size=ins["x0"].shape) * np.array([1, 1, 1, 1, 1, 0, 0, 0, 0.0])
+    ref_moved = cold.solve_batch_host(**moved)
+    got_moved = eng.solve_batch_host(**moved)
+    for got, want in ((again, ref), ({k: v[np.argsort(perm)] for k, v in stale.items()}, ref), (got_moved, ref_moved)):
+        assert np.all(got["status"] == 1) and np.all(want["status"] == 1)
+        scale = np.abs(np.concatenate([want["y_ineq"], want["y_eq"]], 1)).max(1)
+        assert rel_err(got["z"], want["z"]).max() < 1e-8
+        assert rel_err(got["obj"][:, None], want["obj"][:, None]).max() < 1e-8
+        assert (np.abs(got["y_ineq"] - want["y_ineq"]).max(1) / (1 + scale)).max() < 1e-6
+        assert np.array_equal(_active(got["y_ineq"], scale), _active(want["y_ineq"], scale))
 
 
 def test_device_loop_and_run_log(built, cfg, track, tmp_path):
