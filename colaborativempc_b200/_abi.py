@@ -55,7 +55,8 @@ class DmpcBatchIO(C.Structure):
 
 class DmpcShiftIO(C.Structure):
     """dmpc_shift_io: the next DMPC iteration's buffers, written by the solve's own epilogue."""
-    _fields_ = [(k, C.c_void_p) for k in ("x0", "xprev", "uprev", "uold", "xy_send", "hold")]
+    _fields_ = [(k, C.c_void_p) for k in ("x0", "xprev", "uprev", "uold", "xy_send", "hold", "flags", "stop")] + \
+               [("end_s", C.c_double), ("laps", C.c_int32), ("stop_div", C.c_int32)]
 
 
 ENGINE_AUTO, ENGINE_FAST, ENGINE_STAGE = 0, 2, 3
@@ -114,7 +115,7 @@ def default_lib_path():
 EXPORTS = ["dmpc_default_options", "dmpc_version", "dmpc_create", "dmpc_destroy", "dmpc_last_error",
            "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_shift_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
            "dmpc_shift_pack_hold",
-           "dmpc_gather_neighbours", "dmpc_launch_count", "dmpc_engine", "dmpc_sim_batch",
+           "dmpc_gather_neighbours", "dmpc_gather_neighbours_stop", "dmpc_launch_count", "dmpc_engine", "dmpc_sim_batch",
            "dmpc_ocd_lambda_update", "dmpc_ocd_lambda_update_hp"]
 
 _lib = None
@@ -154,6 +155,8 @@ def load_library(path=None):
     lib.dmpc_shift_pack.restype = C.c_int
     lib.dmpc_gather_neighbours.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 5
     lib.dmpc_gather_neighbours.restype = C.c_int
+    lib.dmpc_gather_neighbours_stop.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 6
+    lib.dmpc_gather_neighbours_stop.restype = C.c_int
     lib.dmpc_engine.argtypes = [C.c_void_p]
     lib.dmpc_engine.restype = C.c_int
     lib.dmpc_sim_batch.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 5

@@ -205,6 +205,7 @@ static int solve_impl(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_
   if (next && (!next->x0 || !next->xprev || !next->uprev || !next->uold || !next->xy_send || !next->hold))
     return fail(h, DMPC_ERR_ARG, "dmpc_shift_io: all six buffers are required%s");
   if (next && (!io->z || !io->status) && h->fast) return fail(h, DMPC_ERR_ARG, "the condensed engine shifts from z and status%s");
+  if (next && (next->flags || next->stop) && h->fast) return fail(h, DMPC_ERR_UNSUPPORTED, "stop flags need the stage-wise engine%s");
   CUDA_TRY(h, cudaSetDevice(h->device));
   cudaStream_t st = (cudaStream_t)stream;
   BatchPtrs bp;
@@ -216,7 +217,12 @@ static int solve_impl(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_
   bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
   bp.gws = h->d_gws; bp.gws_stride = h->gws_stride;
   if (!h->fast) {
-    if (next) { bp.nx_x0 = next->x0; bp.nx_xprev = next->xprev; bp.nx_uprev = next->uprev; bp.nx_uold = next->uold; bp.nx_xy = next->xy_send; bp.hold = next->hold; }
+    if (next) {
+      bp.nx_x0 = next->x0; bp.nx_xprev = next->xprev; bp.nx_uprev = next->uprev; bp.nx_uold = next->uold; bp.nx_xy = next->xy_send; bp.hold = next->hold;
+      bp.flags = next->flags; bp.stop = next->stop; bp.stop_div = next->stop_div > 0 ? next->stop_div : 1;
+      bp.laps = next->laps; bp.end_s = next->end_s;
+      if (next->flags && !(next->end_s > 0.0)) return fail(h, DMPC_ERR_ARG, "dmpc_shift_io.flags needs end_s > 0%s");
+    }
     // cost-ordered launch (dmpc_options.order_hint): CTA i solves the QP that was i-th most expensive in the previous
     // call of the same batch size - consecutive MPC steps of a scenario are alike - so the interior-point QPs (8x the mean
     // work) start in the first wave instead of being the tail of the grid.  Scheduling only; results do not change.
@@ -543,23 +549,35 @@ extern "C" int dmpc_shift_pack_hold(dmpc_handle* h, int32_t B, const double* d_z
 
 // xy_all is laid out as ncclAllGather leaves it: [G][S][A_local][T][2] with G = A_total / A_local ranks, i.e. global
 // agent k of scenario s lives at (((k / A_local) * S + s) * A_local + k % A_local).  G = 1 is plain [S][A][T][2].
+// rank_stride: doubles per rank in xy_all (S * A_local * T * 2, plus the flag tail of dmpc_gather_neighbours_stop).
+// stop != nullptr: the tails [S * A_local] of all ranks are reduced into stop[s] (sticky OR over every agent of scenario s).
 __global__ void gather_neighbours_kernel(int S, int A_total, int A_local, int agent_offset, int T, int nn,
-                                         const double* __restrict__ xy_all, const int* __restrict__ nbr_idx,
-                                         double* __restrict__ nbr_xy, double* __restrict__ pose) {
+                                         const double* __restrict__ xy_all, long long rank_stride, const int* __restrict__ nbr_idx,
+                                         double* __restrict__ nbr_xy, double* __restrict__ pose, int* __restrict__ stop) {
   const long long per = (long long)T * (nn + 1);
   const long long total = (long long)S * A_local * per;
+  if (stop) {
+    const int G = A_total / A_local;
+    const long long tail = (long long)S * A_local * T * 2;
+    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < S; s += gridDim.x * blockDim.x) {
+      int any = 0;
+      for (int g = 0; g < G; ++g)
+        for (int a = 0; a < A_local; ++a) any |= xy_all[(size_t)g * rank_stride + tail + (size_t)s * A_local + a] != 0.0;
+      if (any) stop[s] = 1;
+    }
+  }
   for (long long w = blockIdx.x * (long long)blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
     const int b = (int)(w / per);
     const int rem = (int)(w % per), t = rem / (nn + 1), j = rem % (nn + 1);
     const int s = b / A_local, al = b % A_local, ag = agent_offset + al;
-    const double* self = xy_all + ((((size_t)(ag / A_local) * S + s) * A_local + ag % A_local) * T + t) * 2;
+    const double* self = xy_all + (size_t)(ag / A_local) * rank_stride + ((((size_t)s) * A_local + ag % A_local) * T + t) * 2;
     if (j == nn) {
       pose[((size_t)b * T + t) * 2] = self[0]; pose[((size_t)b * T + t) * 2 + 1] = self[1];
     } else {
       const int k = nbr_idx[(size_t)b * nn + j];
       double vx, vy;
       if (k >= 0 && k < A_total) {
-        const double* src = xy_all + ((((size_t)(k / A_local) * S + s) * A_local + k % A_local) * T + t) * 2;
+        const double* src = xy_all + (size_t)(k / A_local) * rank_stride + ((((size_t)s) * A_local + k % A_local) * T + t) * 2;
         vx = src[0]; vy = src[1];
       } else { vx = self[0] + 1e3; vy = self[1] + 1e3; }  // empty slot: geometrically inert, never enters the QP
       double* dst = nbr_xy + (((size_t)b * T + t) * nn + j) * 2;
@@ -568,9 +586,9 @@ __global__ void gather_neighbours_kernel(int S, int A_total, int A_local, int ag
   }
 }
 
-extern "C" int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
-                                      const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
-                                      void* stream) {
+static int launch_gather(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
+                         const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose, int32_t* d_stop,
+                         void* stream) {
   if (!h || !d_xy_all || !d_pose || S < 0 || A_local < 0 || A_total < A_local || agent_offset < 0 ||
       agent_offset + A_local > A_total || (A_local > 0 && A_total % A_local != 0))
     return DMPC_ERR_ARG;
@@ -578,10 +596,24 @@ extern "C" int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total
   const int T = h->P.N + 1, nn = h->P.nn;
   if (nn > 0 && (!d_nbr_idx || !d_nbr_xy)) return DMPC_ERR_ARG;
   const long long total = (long long)S * A_local * T * (nn + 1);
+  const long long rank_stride = (long long)S * A_local * (T * 2 + (d_stop ? 1 : 0));
   const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
   gather_neighbours_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(S, A_total, A_local, agent_offset, T, nn, d_xy_all,
-                                                                     d_nbr_idx, d_nbr_xy, d_pose);
+                                                                     rank_stride, d_nbr_idx, d_nbr_xy, d_pose, d_stop);
   h->launches++;
   CUDA_TRY(h, cudaGetLastError());
   return DMPC_OK;
+}
+
+extern "C" int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
+                                      const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
+                                      void* stream) {
+  return launch_gather(h, S, A_total, A_local, agent_offset, d_xy_all, d_nbr_idx, d_nbr_xy, d_pose, nullptr, stream);
+}
+
+extern "C" int dmpc_gather_neighbours_stop(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
+                                           const double* d_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
+                                           int32_t* d_stop, void* stream) {
+  if (!d_stop) return h ? fail(h, DMPC_ERR_ARG, "dmpc_gather_neighbours_stop needs d_stop%s") : DMPC_ERR_ARG;
+  return launch_gather(h, S, A_total, A_local, agent_offset, d_all, d_nbr_idx, d_nbr_xy, d_pose, d_stop, stream);
 }

@@ -171,6 +171,12 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
     } else if (Q3_LANE == 0 && io.hold) {
       io.hold[b] += 1;
     }
+    if (io.flags && Q3_LANE == 0) {  // utilities/misc.py:28-48 on row 0 of this prediction (= the state solved from)
+      const double s = hd->x0[6], L = io.end_s;
+      const bool near = fabs(s - L) <= 0.15 + 1e-5 * fabs(L) || s > L;   // np.isclose(s, L, atol=0.15) or s > L
+      const bool ended = near && floor(s / L) == (double)io.laps;
+      io.flags[b] = (ended ? 1.0 : 0.0) + (feas ? 0.0 : 2.0);
+    }
   }
 }
 
@@ -179,6 +185,7 @@ __global__ void __launch_bounds__(QP3_THREADS) lpv_qp_stage_kernel(const __grid_
   if ((int)blockIdx.x >= io.B) return;
   const int b = io.order ? io.order[blockIdx.x] : blockIdx.x;  // most expensive QPs of the previous call first
   if (io.only_status && io.status[b] != io.only_status) return;
+  if (io.stop && io.stop[b / io.stop_div]) return;  // the scenario's experiment is over: nothing of it changes any more
   solve_one_qp3(P, io, b);
 }
 #endif

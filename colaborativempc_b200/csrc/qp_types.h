@@ -57,5 +57,9 @@ struct BatchPtrs {
   int warm_shift;
   double *nx_x0, *nx_xprev, *nx_uprev, *nx_uold, *nx_xy;
   int* hold;
+  double* flags;            // [B] 1 * ended + 2 * failed (dmpc_shift_io.flags)
+  const int* stop;          // per-scenario stop (dmpc_shift_io.stop), scenario of QP b = b / stop_div
+  int stop_div, laps;
+  double end_s;
 };
 

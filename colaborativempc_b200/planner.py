@@ -56,6 +56,8 @@ class BatchedPlannerLPV(object):
         self.engine = self.lib.dmpc_engine(self._h)      # _abi.ENGINE_STAGE (qp3_*.cuh) or _abi.ENGINE_FAST (qp2_*.cuh)
         self.fast = self.engine == _abi.ENGINE_FAST
         self.n = 16 * self.N + 12
+        ns = int(self.params.nseg)
+        self.track_length = float(self.params.seg_s0[ns - 1] + self.params.seg_len[ns - 1])  # Map.TrackLength
         self.m_in = (8 + self.nn) * self.N
         self.m_eq = 14 * self.N + 12
 
@@ -111,7 +113,8 @@ class BatchedPlannerLPV(object):
                     shift=None):
         """Asynchronous on `stream` (default: torch's current stream).  Returns the dict of output tensors.
         shift: dict(x0, xprev [B,N,9], uprev, uold, xy_send [B,N+1,2], hold int32 [B]) of CUDA tensors - the next DMPC
-        iteration's buffers, written by the solve's own epilogue (dmpc_solve_shift_batch; LPV_HP_N_main.py:102-117)."""
+        iteration's buffers, written by the solve's own epilogue (dmpc_solve_shift_batch; LPV_HP_N_main.py:102-117);
+        optional flags [B] float64 (with end_s, laps) and stop int32 [B / stop_div] (with stop_div): dmpc_shift_io."""
         torch = _torch()
         B, rows = x0.shape[0], xprev.shape[1]
         ins = dict(x0=x0, xprev=xprev, uprev=uprev, uold=uold, nbr_xy=nbr_xy, pose=pose, nbr_count=nbr_count)
@@ -129,14 +132,19 @@ class BatchedPlannerLPV(object):
         if shift is None:
             self._check(self.lib.dmpc_solve_batch(self._h, C.byref(io), C.c_void_p(s.cuda_stream)))
             return out
-        shapes = dict(x0=(B, 9), xprev=(B, self.N, 9), uprev=(B, self.N, 2), uold=(B, 2), xy_send=(B, self.N + 1, 2), hold=(B,))
+        div = int(shift.get("stop_div", 1))
+        shapes = dict(x0=(B, 9), xprev=(B, self.N, 9), uprev=(B, self.N, 2), uold=(B, 2), xy_send=(B, self.N + 1, 2), hold=(B,),
+                      flags=(B,), stop=((B + div - 1) // div,))
         sh = DmpcShiftIO()
         for k, shp in shapes.items():
-            t = shift[k]
-            want = torch.int32 if k == "hold" else torch.float64
+            t = shift.get(k)
+            if t is None and k in ("flags", "stop"):
+                continue
+            want = torch.int32 if k in ("hold", "stop") else torch.float64
             if not (t.is_cuda and t.dtype == want and t.is_contiguous() and tuple(t.shape) == shp):
                 raise DmpcError("shift[%s] must be a contiguous CUDA %s tensor of shape %s" % (k, want, shp))
             setattr(sh, k, t.data_ptr())
+        sh.end_s, sh.laps, sh.stop_div = float(shift.get("end_s", 0.0)), int(shift.get("laps", 1)), div
         self._check(self.lib.dmpc_solve_shift_batch(self._h, C.byref(io), C.byref(sh), C.c_void_p(s.cuda_stream)))
         return out
 
@@ -174,12 +182,17 @@ class BatchedPlannerLPV(object):
         self._check(self.lib.dmpc_shift_pack_hold(self._h, z.shape[0], p(z), p(status), p(x0), p(xprev), p(uprev), p(uold),
                                                   p(xy_send), p(hold), C.c_void_p(s.cuda_stream)))
 
-    def gather_neighbours(self, xy_all, nbr_idx, nbr_xy, pose, S, A_total, A_local, agent_offset, stream=None):
+    def gather_neighbours(self, xy_all, nbr_idx, nbr_xy, pose, S, A_total, A_local, agent_offset, stream=None, stop=None):
+        """stop (int32 [S]): xy_all is the all-gathered payload WITH the flag tails (dmpc_gather_neighbours_stop)."""
         torch = _torch()
         s = torch.cuda.current_stream(self.device) if stream is None else stream
         p = lambda t: None if t is None else t.data_ptr()
-        self._check(self.lib.dmpc_gather_neighbours(self._h, S, A_total, A_local, agent_offset, p(xy_all), p(nbr_idx),
-                                                    p(nbr_xy), p(pose), C.c_void_p(s.cuda_stream)))
+        if stop is None:
+            self._check(self.lib.dmpc_gather_neighbours(self._h, S, A_total, A_local, agent_offset, p(xy_all), p(nbr_idx),
+                                                        p(nbr_xy), p(pose), C.c_void_p(s.cuda_stream)))
+        else:
+            self._check(self.lib.dmpc_gather_neighbours_stop(self._h, S, A_total, A_local, agent_offset, p(xy_all), p(nbr_idx),
+                                                             p(nbr_xy), p(pose), p(stop), C.c_void_p(s.cuda_stream)))
 
 
     def sim_batch(self, xpred, u, out=None, status=None, stream=None):

@@ -57,28 +57,30 @@ class RunLog(object):
         return path
 
 
-def run_closed_loop(dm, track_length, max_it, laps=1, logs=None, log_scenario=0, warn_slack=True):
-    """LPV_HP_N_main.py:96-120 around a `ShardedDMPC`: iterate until `max_it`, until ANY logged agent's QP is infeasible
-    (the reference breaks on the first `not feas`), or until the logged scenario has ended (`check_end`).
+def run_closed_loop(dm, max_it, logs=None, log_scenario=0, warn_slack=True):
+    """LPV_HP_N_main.py:96-120 around a `ShardedDMPC`: iterate until `max_it`, until ANY agent of the logged scenario - on
+    any rank - has a QP that is not feasible (the reference breaks on the first `not feas`, before it records the
+    iteration), or until any of them is at the end of the track (`checkEnd` with the track length `dm.end_s`, evaluated
+    like the reference on row 0 of the last prediction, before the next iteration).  Both conditions are read from the
+    flags that travelled with the exchange, so every rank takes the same decision on the same iteration.
     logs: list of `RunLog`, one per local agent of scenario `log_scenario` (rows [log_scenario*A_local, +A_local) of the
     batch); per iteration only that scenario's solution (A_local x (16N+12) doubles) crosses PCIe.
     Returns (iterations done, ended, error)."""
-    torch = dm.torch
     N, al = dm.N, dm.a_local
     rows = slice(log_scenario * al, (log_scenario + 1) * al)
     it, error, ended = 0, False, False
-    s_now = dm.x0[rows, 6].cpu().numpy()[None, :]
-    while it < max_it and not check_end(s_now, track_length, laps)[0]:
+    while it < max_it and not ended:
         tic = time.time()
         out = dm.iterate()
         z = out["z"][rows].cpu().numpy()  # synchronises the stream
         st = out["status"][rows].cpu().numpy()
         pl = out["planes"][rows].cpu().numpy()
         dt_op = (time.time() - tic) / max(dm.B, 1)
-        feas = np.isin(st, (1, 2, -2))  # LPV_Planner.py:246-248
-        if not feas.all():
+        ended_now, failed = dm.scenario_flags(log_scenario)   # of this iteration, over all ranks
+        if failed:
             error = True
             break
+        feas = np.isin(st, (1, 2, -2))  # LPV_Planner.py:246-248 (all true here: a local failure raises the flag)
         xs = z[:, :12 * (N + 1)].reshape(al, N + 1, 12)
         x_pred, s_pred = xs[:, :, :9], xs[:, 1:, 9:]
         u_pred = z[:, 12 * (N + 1):12 * (N + 1) + 2 * N].reshape(al, N, 2)
@@ -88,7 +90,6 @@ def run_closed_loop(dm, track_length, max_it, laps=1, logs=None, log_scenario=0,
             for a, lg in enumerate(logs):
                 lg.time_op.append(dt_op)
                 lg.save(x_pred[a], u_pred[a], int(feas[a]), pl[a])
-        s_now = x_pred[None, :, 0, 6]
         it += 1
-    ended = bool(check_end(s_now, track_length, laps)[0])
+        ended = ended_now
     return it, ended, error

@@ -126,7 +126,7 @@ typedef struct dmpc_batch_io {
 } dmpc_batch_io;
 
 /* Buffers of the NEXT DMPC iteration, written by the solve's own epilogue (dmpc_solve_shift_batch): the caller's
- * bookkeeping of planner/scripts/LPV_HP_N_main.py:102-117 and LPV_Planner.py:179-180.  A pointer may alias the same
+ * bookkeeping of planner/scripts/LPV_HP_N_main.py:96-117 and LPV_Planner.py:179-180.  A pointer may alias the same
  * input of the call (x0 / xprev with xprev_rows == N / uprev / uold): a QP only ever touches its own rows. */
 typedef struct dmpc_shift_io {
   double* x0;        /* [B,9]      <- xPred[1]                              LPV_HP_N_main.py:106 */
@@ -136,7 +136,16 @@ typedef struct dmpc_shift_io {
   double* xy_send;   /* [B,N+1,2]  <- xPred[:,7:9], packed for the exchange LPV_HP_N_main.py:117 */
   int32_t* hold;     /* [B] in/out: consecutive failed solves of this QP.  feasible (LPV_Planner.py:246-248) -> 0 and the
                         buffers above receive this call's plan; otherwise +1 and the buffers keep the last valid plan (the
-                        reference breaks its loop here, LPV_HP_N_main.py:102-104; the caller reads hold to stop the scenario) */
+                        reference breaks its loop here, LPV_HP_N_main.py:102-104)                                         */
+  /* optional (stage-wise engine): the reference's two stop conditions, per QP, for the caller's per-scenario stop */
+  double* flags;     /* [B] or NULL: 1.0 * ended + 2.0 * failed.  ended = checkEnd (utilities/misc.py:28-48) on the state
+                        this solve started from: s within 0.15 m (np.isclose) of end_s or beyond it, on lap `laps`;
+                        failed = this solve was not feasible.  Laid out to travel with xy_send in the same all-gather.     */
+  const int32_t* stop; /* [ceil(B / stop_div)] or NULL: QPs of a stopped scenario (stop[b / stop_div] != 0) are skipped: none
+                        of their buffers, outputs or flags change (the experiment is over, LPV_HP_N_main.py:96,110-111)    */
+  double end_s;      /* track length the end rule compares with (Map.TrackLength)                                          */
+  int32_t laps;      /* lap number that ends the run (checkEnd's `laps`, 1 in the reference)                               */
+  int32_t stop_div;  /* QPs per scenario in this batch (local agents)                                                      */
 } dmpc_shift_io;
 
 typedef struct dmpc_handle dmpc_handle;
@@ -190,6 +199,16 @@ int dmpc_shift_pack_hold(dmpc_handle* h, int32_t B, const double* d_z, const int
 int dmpc_gather_neighbours(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
                            const double* d_xy_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
                            void* stream);
+
+/* dmpc_gather_neighbours on a payload that carries the stop flags: every rank sends
+ *   [ xy_send (S * A_local * (N+1) * 2 doubles) | flags (S * A_local doubles, dmpc_shift_io.flags) ],
+ * so d_all is [G][S * A_local * ((N+1) * 2 + 1)].  Besides the gather, d_stop[s] (int32 [S], in/out, sticky) is set for
+ * every scenario with ANY agent on ANY rank ended or failed - the reference's loop condition and break
+ * (LPV_HP_N_main.py:96,102-104,110-111; checkEnd returns at the first agent that is at the end).  Every rank computes
+ * the same d_stop from the same gathered buffer: no extra collective, no rank can leave the loop alone. */
+int dmpc_gather_neighbours_stop(dmpc_handle* h, int32_t S, int32_t A_total, int32_t A_local, int32_t agent_offset,
+                                const double* d_all, const int32_t* d_nbr_idx, double* d_nbr_xy, double* d_pose,
+                                int32_t* d_stop, void* stream);
 
 /* Batched LPV model roll-out, SURVEY.md 8(f2).  Replaces LPV_Model.sim (LPV_val.py:77-94) with that file's own
  * linearisation (LPV_val.py:96-195: no low-velocity branch) for B independent models, DEVICE buffers:

@@ -16,7 +16,8 @@ SRCS = [os.path.join(HERE, "qp3_host.cpp")] + [os.path.join(CSRC, f) for f in
 
 
 class ShiftIO(C.Structure):
-    _fields_ = [(k, C.c_void_p) for k in ("x0", "xprev", "uprev", "uold", "xy_send", "hold")]
+    _fields_ = [(k, C.c_void_p) for k in ("x0", "xprev", "uprev", "uold", "xy_send", "hold", "flags", "stop")] + \
+               [("end_s", C.c_double), ("laps", C.c_int32), ("stop_div", C.c_int32)]
 
 
 def build(force=False):
@@ -48,7 +49,7 @@ def default_options():
 
 
 def solve_batch(params, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, options=None, shift=False, warm=None,
-                warm_shift=0):
+                warm_shift=0, end_s=0.0, stop=None, stop_div=1):
     """warm: uint8 [B, (8+nn)N] working sets, read as first guesses and overwritten with the certified ones."""
     N, nn = params.N, params.nn
     f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
@@ -73,8 +74,13 @@ def solve_batch(params, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, op
         if rows == N:
             nx["xprev"][:] = xprev
         sh = ShiftIO()
+        if end_s > 0:
+            nx["flags"] = np.full(B, -1.0)
+        if stop is not None:
+            nx["stop"] = np.ascontiguousarray(stop, dtype=np.int32)
         for k, a in nx.items():
             setattr(sh, k, p(a))
+        sh.end_s, sh.laps, sh.stop_div = float(end_s), 1, int(stop_div)
         out["next"] = nx
     o = options or default_options()
     if warm is not None:

@@ -30,7 +30,8 @@ extern "C" int qp3_host_solve_batch(const dmpc_params* p, const dmpc_options* op
   bp.nbr_count = io->nbr_count;
   bp.z = io->z; bp.planes = io->planes; bp.y_ineq = io->y_ineq; bp.y_eq = io->y_eq; bp.obj = io->obj;
   bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
-  if (sh) { bp.nx_x0 = sh->x0; bp.nx_xprev = sh->xprev; bp.nx_uprev = sh->uprev; bp.nx_uold = sh->uold; bp.nx_xy = sh->xy_send; bp.hold = sh->hold; }
+  if (sh) { bp.nx_x0 = sh->x0; bp.nx_xprev = sh->xprev; bp.nx_uprev = sh->uprev; bp.nx_uold = sh->uold; bp.nx_xy = sh->xy_send; bp.hold = sh->hold;
+            bp.flags = sh->flags; bp.stop = sh->stop; bp.stop_div = sh->stop_div > 0 ? sh->stop_div : 1; bp.laps = sh->laps; bp.end_s = sh->end_s; }
   bp.warm = warm; bp.warm_shift = warm_shift;
   const size_t park = stage_park_doubles(P.N, P.nn);
   std::vector<double> gws((size_t)io->B * park);
@@ -44,6 +45,7 @@ extern "C" int qp3_host_solve_batch(const dmpc_params* p, const dmpc_options* op
 #pragma omp for schedule(dynamic, 1)
     for (int b = 0; b < io->B; ++b) {
       memset(ws, 0, bytes);
+      if (bp.stop && bp.stop[b / bp.stop_div]) continue;
       solve_one_qp3(P, bp, b);
       if (counters) {
         const Hdr3* hd = (const Hdr3*)ws;

@@ -364,19 +364,27 @@ def test_device_loop_and_run_log(built, cfg, track, tmp_path):
     S, A, iters = 4, 3, 5
     x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=300)
     idx, cnt = sc.topology(A, "full")
-    rec, host_eng = [], _engine(cfg, track, max_batch=S * A)
-    sc.run_dmpc(lambda **kw: host_eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, iters, N, record=rec)
+    # the host loop on a handle with the same carried state as ShardedDMPC's (warm start moved one stage per step)
+    rec, host_eng = [], _engine(cfg, track, max_batch=S * A, options={"warm_start": 2})
+    sc.run_dmpc(lambda **kw: host_eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, iters + 3, N, record=rec)
     dm = ShardedDMPC(_engine(cfg, track, max_batch=S * A), S, A, idx, cnt, x0, xprev, uprev)
     for it in range(iters):
         out = dm.iterate()
         torch.cuda.synchronize()
         assert np.array_equal(out["z"].cpu().numpy(), rec[it][1]["z"]), it
         assert np.array_equal(out["status"].cpu().numpy(), rec[it][1]["status"])
+    assert not dm.stopped().any() and int(dm.hold.sum()) == 0
+    # the same iteration as ONE CUDA graph (gather -> solve + bookkeeping -> launch order -> exchange): same bits
+    dm.capture()
+    for it in range(iters, iters + 3):
+        out = dm.iterate()
+        torch.cuda.synchronize()
+        assert np.array_equal(out["z"].cpu().numpy(), rec[it][1]["z"]), it
     # the logged run: scenario 1, a track "ending" 0.6 m ahead of the leading agent so that the end rule fires
-    dm = ShardedDMPC(_engine(cfg, track, max_batch=S * A), S, A, idx, cnt, x0, xprev, uprev)
-    logs = [RunLog(a, str(tmp_path) + "/") for a in range(A)]
     L = float(x0[1, :, 6].max()) + 0.6
-    n_it, ended, error = run_closed_loop(dm, L, 200, logs=logs, log_scenario=1)
+    dm = ShardedDMPC(_engine(cfg, track, max_batch=S * A), S, A, idx, cnt, x0, xprev, uprev, end_s=L)
+    logs = [RunLog(a, str(tmp_path) + "/") for a in range(A)]
+    n_it, ended, error = run_closed_loop(dm, 200, logs=logs, log_scenario=1)
     assert ended and not error and 0 < n_it < 200
     zs = [r[1]["z"].reshape(S, A, -1)[1] for r in rec]
     for a, lg in enumerate(logs):
@@ -390,6 +398,49 @@ def test_device_loop_and_run_log(built, cfg, track, tmp_path):
         assert np.loadtxt(path + "/states.dat").reshape(n_it, 9).shape == (n_it, 9)
     s_last = max(lg.states[-1][6] for lg in logs)
     assert s_last < L + 0.5  # stopped at the first iteration whose row 0 passed L - 0.15
+
+
+def test_failed_solve_holds_the_plan_and_stops_the_scenario(built, cfg, track):
+    """LPV_HP_N_main.py:102-104,110-111: the reference stops an experiment at the first QP that is not feasible.  Here a
+    failed QP (its map lookup is made to fail, where the reference raises) keeps its last valid plan, nothing non-finite
+    enters the exchange, its scenario is flagged and frozen from the next iteration on - on every rank, because the flag
+    travels with the all-gather - and the other scenarios run on."""
+    import torch
+    from colaborativempc_b200 import scenarios as sc
+    from colaborativempc_b200.dmpc import ShardedDMPC
+    S, A = 6, 3
+    x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=400)
+    idx, cnt = sc.topology(A, "full")
+    dm = ShardedDMPC(_engine(cfg, track, max_batch=S * A), S, A, idx, cnt, x0, xprev, uprev)
+    for _ in range(3):
+        dm.iterate()
+    assert not dm.stopped().any()
+    bad = 2 * A + 1                                   # scenario 2, agent 1
+    L = float(np.ravel(track.TrackLength)[0])
+    keep = {k: getattr(dm, k).clone() for k in ("x0", "xprev", "uprev", "uold", "xy_send")}
+    dm.xprev[bad, 5, 6] = L                           # curvature() finds no segment for s == TrackLength (misc.py:97)
+    out = dm.iterate()
+    torch.cuda.synchronize()
+    st = out["status"].cpu().numpy()
+    assert st[bad] == -20 and np.all(np.delete(st, bad) == 1)
+    assert int(dm.hold[bad]) == 1 and int(dm.hold.sum()) == 1
+    for k in ("x0", "uprev", "uold", "xy_send"):      # the failed agent keeps its last valid plan ...
+        assert torch.equal(getattr(dm, k)[bad], keep[k][bad]), k
+    assert torch.isfinite(dm.send).all() and torch.isfinite(dm.all).all()   # ... and nothing non-finite is exchanged
+    assert dm.scenario_flags(2) == (False, True) and dm.scenario_flags(1) == (False, False)
+    stop = dm.stopped()
+    assert stop.tolist() == [False, False, True, False, False, False]
+    frozen = {k: getattr(dm, k).clone() for k in ("x0", "xprev", "uprev", "uold", "xy_send")}
+    for _ in range(3):
+        out = dm.iterate()
+    torch.cuda.synchronize()
+    rows = slice(2 * A, 3 * A)
+    for k, v in frozen.items():                       # the stopped scenario does not move any more, the others do
+        assert torch.equal(getattr(dm, k)[rows], v[rows]), k
+        assert not torch.equal(getattr(dm, k)[:A], v[:A]), k
+    st = out["status"].cpu().numpy()
+    assert np.all(np.delete(st, np.arange(2 * A, 3 * A)) == 1)
+    assert dm.stopped().tolist() == [False, False, True, False, False, False]
 
 
 def test_model_rollout_vs_reference_and_oracle(built, cfg, track):
