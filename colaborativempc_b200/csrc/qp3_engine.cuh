@@ -615,7 +615,10 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
 // Backward pass for a new gradient with the factor kept from ric_factor_backward3 (zero defects).  One phase per stage.
 // ye != nullptr: the costates are written as the multipliers of the dynamics rows (rows of G, LPV_Planner.py:429-475):
 // ye[12 t + j] = -px_t[j], t = N .. 1, and row block 0 from one adjoint step (gq0 = gradient of the cost in x_0).
-Q3D void ric_affine_backward3(const Ctx3& c, double* ye) {
+// fb = 0: no feedback term (z = 0), i.e. the plain adjoint recursion px_k = A_k' px_{k+1} + gx_{k-1}: the costates that make
+// the state rows of the stationarity condition hold exactly at ANY point (used when no working set was certified and
+// the kept factor does not belong to the returned iterate).
+Q3D void ric_affine_backward3(const Ctx3& c, double* ye, const int fb = 1) {
   Hdr3* hd = c.hd;
   const int N = c.N;
   const double* dR2 = hd->dR2;
@@ -633,7 +636,7 @@ Q3D void ric_affine_backward3(const Ctx3& c, double* ye) {
     const double hu0 = c.gu[2 * k] + pvin[0] + fma(B[0], pin[0], fma(B[1], pin[1], B[2] * pin[2]));
     const double hu1 = c.gu[2 * k + 1] + pvin[1] + B[3] * pin[0];
     const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
-    const double z0 = W00 * hu0 + W01 * hu1, z1 = W01 * hu0 + W11 * hu1;
+    const double z0 = fb ? W00 * hu0 + W01 * hu1 : 0.0, z1 = fb ? W01 * hu0 + W11 * hu1 : 0.0;
     Q3_ITEM(j, 9) {
       double v = pin[j];
       if (j < 3) {

@@ -132,7 +132,7 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
     if (io.y_eq) {
       double* ye = io.y_eq + (size_t)b * (14 * N + 12);
       assemble_gradient3(c, G3_LAG, 0.0);
-      ric_affine_backward3(c, ye);
+      ric_affine_backward3(c, ye, status == DMPC_SOLVED);
       Q3_FOR(t, N + 1) { ye[12 * t + 9] = 0.0; ye[12 * t + 10] = 0.0; ye[12 * t + 11] = 0.0; }
       Q3_FOR(k, N) {
         const double d0 = c.u[2 * k] - (k == 0 ? hd->uold[0] : c.u[2 * k - 2]);

@@ -145,7 +145,8 @@ class ShardedDMPC(object):
     def capture(self):
         """Captures one iteration (gather -> solve+bookkeeping -> launch-order kernel -> all-gather) into a CUDA graph;
         `iterate` replays it from then on.  Call after at least two eager iterations (the first one reads the N+1-row
-        history, and the handle settles its launch-order / warm-start state on the first call of a batch size)."""
+        history, and the handle settles its launch-order / warm-start state on the first call of a batch size).  The call
+        itself advances the loop by ONE iteration (the warm-up run CUDA graphs need), whose outputs are in `self.out`."""
         torch = self.torch
         if self.first:
             raise RuntimeError("capture() after the first iteration")

@@ -62,10 +62,12 @@ typedef struct dmpc_options {
   int32_t engine;         /* dmpc_engine: 0 auto (the stage-wise engine), 2 condensed engine (workspace packed in shared memory;
                              dmpc_create fails if the horizon does not fit; QPs whose condensed Hessian cannot be factorised
                              are re-solved stage-wise in the same call), 3 stage-wise engine (any horizon)           */
-  int32_t order_hint;     /* fast engine: 1 = a call orders and splits its launch by what the previous call of the same
-                             batch size spent on each QP index (most expensive first, the interior-point ones alone on
-                             an SM; consecutive MPC steps are alike).  Scheduling only: results are independent of it.
-                             Calls on one handle must then be stream-ordered with each other.  0 = off               */
+  int32_t order_hint;     /* 1 = a call uses what the previous call of the same batch size spent on each QP index (consecutive
+                             MPC steps are alike): the launch starts the most expensive QPs first, and a QP that ended in the
+                             interior point last time goes there after two active-set rounds instead of twelve (stage-wise
+                             engine; the condensed engine also splits its launch).  The certified optimum is the same; the
+                             route to it - hence the last bits and the iteration counts - may differ.  Calls on one handle
+                             must be stream-ordered with each other.  0 = off                                              */
   int32_t host_direct;    /* dmpc_solve_batch_host: 1 = when every buffer of the call is page-locked host memory
                              (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory) the kernel reads and writes it
                              in place over PCIe instead of staging copies; pageable buffers always take the staged

@@ -194,8 +194,8 @@ def test_page_locked_host_buffers_are_used_in_place(built, cfg, track):
     import torch
     fx = golden("platoon_N20.npz")
     ins = {k: fx["it3_%s" % k] for k in INPUT_KEYS}
-    staged = _engine(cfg, track, options={"host_direct": 0, "warm_start": 0}).solve_batch_host(**ins)
-    eng = _engine(cfg, track, options={"warm_start": 0})
+    staged = _engine(cfg, track, options={"host_direct": 0, "warm_start": 0, "order_hint": 0}).solve_batch_host(**ins)
+    eng = _engine(cfg, track, options={"warm_start": 0, "order_hint": 0})  # bit-for-bit: nothing carried between calls
     B = ins["x0"].shape[0]
 
     def pinned(a, pad=0):  # a copy of `a` living `pad` elements into a page-locked allocation
@@ -296,7 +296,7 @@ def test_full_size_batch_properties(built, cfg, track):
     import torch
     from colaborativempc_b200 import scenarios as sc
     S, A = 64, 3
-    eng = _engine(cfg, track, max_batch=4096, options={"warm_start": 0})  # bitwise properties: no carried guesses
+    eng = _engine(cfg, track, max_batch=4096, options={"warm_start": 0, "order_hint": 0})  # bitwise properties: nothing carried
     x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=1000)
     idx, cnt = sc.topology(A, "full")
     st = sc.run_dmpc(lambda **kw: eng.solve_batch_host(**kw), x0, xprev, uprev, idx, cnt, 3, N)
@@ -375,8 +375,10 @@ def test_device_loop_and_run_log(built, cfg, track, tmp_path):
         assert np.array_equal(out["status"].cpu().numpy(), rec[it][1]["status"])
     assert not dm.stopped().any() and int(dm.hold.sum()) == 0
     # the same iteration as ONE CUDA graph (gather -> solve + bookkeeping -> launch order -> exchange): same bits
-    dm.capture()
-    for it in range(iters, iters + 3):
+    dm.capture()   # runs one more iteration eagerly (on the capture stream), then records the next one
+    torch.cuda.synchronize()
+    assert np.array_equal(dm.out["z"].cpu().numpy(), rec[iters][1]["z"])
+    for it in range(iters + 1, iters + 3):
         out = dm.iterate()
         torch.cuda.synchronize()
         assert np.array_equal(out["z"].cpu().numpy(), rec[it][1]["z"]), it
