@@ -115,7 +115,7 @@ def default_lib_path():
 EXPORTS = ["dmpc_default_options", "dmpc_version", "dmpc_create", "dmpc_destroy", "dmpc_last_error",
            "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_shift_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
            "dmpc_shift_pack_hold",
-           "dmpc_gather_neighbours", "dmpc_gather_neighbours_stop", "dmpc_launch_count", "dmpc_engine", "dmpc_sim_batch",
+           "dmpc_gather_neighbours", "dmpc_gather_neighbours_stop", "dmpc_launch_count", "dmpc_smem_bytes", "dmpc_engine", "dmpc_sim_batch",
            "dmpc_ocd_lambda_update", "dmpc_ocd_lambda_update_hp"]
 
 _lib = None
@@ -167,6 +167,8 @@ def load_library(path=None):
     lib.dmpc_ocd_lambda_update_hp.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_void_p, C.c_void_p,
                                               C.c_void_p, C.c_void_p]
     lib.dmpc_ocd_lambda_update_hp.restype = C.c_int
+    lib.dmpc_smem_bytes.argtypes = [C.c_void_p]
+    lib.dmpc_smem_bytes.restype = C.c_int64
     lib.dmpc_launch_count.argtypes = [C.c_void_p]
     lib.dmpc_launch_count.restype = C.c_int64
     if path == default_lib_path():

@@ -187,6 +187,8 @@ extern "C" int dmpc_set_options(dmpc_handle* h, const dmpc_options* opt) {
 
 extern "C" int dmpc_engine(const dmpc_handle* h) { return h ? (h->fast ? DMPC_ENGINE_FAST : DMPC_ENGINE_STAGE) : 0; }
 
+extern "C" int64_t dmpc_smem_bytes(const dmpc_handle* h) { return h ? (int64_t)(h->fast ? h->smem_bytes : h->stage_smem) : 0; }
+
 extern "C" int64_t dmpc_launch_count(const dmpc_handle* h) { return h ? h->launches : 0; }
 
 static int launch_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, const int32_t* d_status, double* d_x0,

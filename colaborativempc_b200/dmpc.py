@@ -116,6 +116,7 @@ class ShardedDMPC(object):
         self.laps = int(laps)
         self.first = True
         self.graph = None
+        self.launches_per_iteration = 3 if self.fused else 6
         self.exchange()
 
     def _shift(self):
@@ -152,8 +153,10 @@ class ShardedDMPC(object):
             raise RuntimeError("capture() after the first iteration")
         s = torch.cuda.Stream(device=self.eng.device)
         s.wait_stream(torch.cuda.current_stream(self.eng.device))
+        n0 = self.eng.launches
         with torch.cuda.stream(s):
             self._body(self.xprev)
+        self.launches_per_iteration = self.eng.launches - n0   # kernels of this library in one iteration (= in one replay)
         torch.cuda.current_stream(self.eng.device).wait_stream(s)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):

@@ -80,6 +80,10 @@ class BatchedPlannerLPV(object):
     def launches(self):
         return int(self.lib.dmpc_launch_count(self._h))
 
+    def stage_smem_bytes(self):
+        """Dynamic shared memory per QP (one CTA) of the handle's engine."""
+        return int(self.lib.dmpc_smem_bytes(self._h))
+
     def set_options(self, **kw):
         for k, v in kw.items():
             setattr(self.options, k, v)

@@ -242,6 +242,9 @@ int dmpc_ocd_lambda_update_hp(dmpc_handle* h, int32_t S, int32_t A, double alpha
 /* Engine the handle runs on: DMPC_ENGINE_STAGE or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
 int dmpc_engine(const dmpc_handle* h);
 
+/* Dynamic shared memory one QP's CTA asks for on the handle's engine (the whole per-QP workspace lives there). */
+int64_t dmpc_smem_bytes(const dmpc_handle* h);
+
 /* Number of kernels the handle has launched so far (bench.py's gpu_launches claim). */
 int64_t dmpc_launch_count(const dmpc_handle* h);
 

@@ -1,16 +1,20 @@
 #!/bin/bash
-# One GPU-box session (round 2): GPU tests, config[1] bench on both engines / warm start on-off.  Logs under gpurun_out/.
+# One GPU-box session (round 2): GPU tests, bench N=1 (full line), bench DMPC on one GPU, roofline counts.
 T=${1:-r02a}
 mkdir -p gpurun_out
 (timeout 900 python -m pytest tests -m gpu -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest.log)
-for cfgs in "3 1" "3 0" "2 1"; do set -- $cfgs
-timeout 300 python bench.py --steps 20 --warmup 3 --engine $1 --warm $2 --no-cpu-baseline > gpurun_out/${T}_bench_e$1_w$2.log 2>&1; echo "rc=$?" >> gpurun_out/${T}_bench_e$1_w$2.log
-done
-tail -n 30 gpurun_out/${T}_pytest.log | cut -c1-250
-for f in gpurun_out/${T}_bench_e*.log; do echo $f; tail -n 2 $f | python -c "
-import sys, json
-for l in sys.stdin:
-    try: d = json.loads(l)
-    except Exception: print(l[:300]); continue
-    print({k: d[k] for k in ('value','ms_per_step','solved','qp_local','ipm_iters_mean','polish_rounds_mean','gpu_launches')}, 'e2e', d['e2e']['value'], 'unordered', d.get('unordered'))
-"; done
+tail -n 25 gpurun_out/${T}_pytest.log | cut -c1-250
+timeout 900 python bench.py --steps 20 --warmup 3 > gpurun_out/${T}_bench_n1.json 2> gpurun_out/${T}_bench_n1.err; echo "bench n1 rc=$?"; tail -3 gpurun_out/${T}_bench_n1.err
+timeout 600 python bench.py --workload dmpc --steps 20 --warmup 3 > gpurun_out/${T}_bench_dmpc1.json 2> gpurun_out/${T}_bench_dmpc1.err; echo "bench dmpc rc=$?"; tail -3 gpurun_out/${T}_bench_dmpc1.err
+bash scripts/gpu_roofline.sh
+python - "$T" <<'PY'
+import json,glob,sys
+for f in sorted(glob.glob("gpurun_out/%s_bench_*.json" % sys.argv[1] if len(sys.argv)>1 else "gpurun_out/*_bench_*.json")):
+    try: d=json.loads(open(f).read().strip().split("\n")[-1])
+    except Exception as e: print(f, "unparsable", e); continue
+    print(f, {k: d.get(k) for k in ("value","ms_per_step","solved","qp_timed","infeasible","ipm_iters_mean","polish_rounds_mean","gpu_launches")})
+    for k in ("replay","cold","e2e","weak_baseline","step_breakdown_ms","config3","cpu_baseline"): 
+        if d.get(k): print("   ", k, json.dumps(d[k])[:700])
+    if d.get("sweep"):
+        for s in d["sweep"]: print("    sweep", json.dumps(s)[:600])
+PY

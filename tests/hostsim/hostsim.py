@@ -49,7 +49,7 @@ def default_options():
 
 
 def solve_batch(params, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, options=None, shift=False, warm=None,
-                warm_shift=0, end_s=0.0, stop=None, stop_div=1):
+                warm_shift=0, end_s=0.0, stop=None, stop_div=1, cost=None):
     """warm: uint8 [B, (8+nn)N] working sets, read as first guesses and overwritten with the certified ones."""
     N, nn = params.N, params.nn
     f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
@@ -87,7 +87,7 @@ def solve_batch(params, x0, xprev, uprev, uold, nbr_xy, pose, nbr_count=None, op
         assert warm.dtype == np.uint8 and warm.flags.c_contiguous and warm.shape == (B, mi)
     rc = lib().qp3_host_solve_batch(C.byref(params), C.byref(o), C.byref(io), C.byref(sh) if sh is not None else None,
                                     counters.ctypes.data_as(C.c_void_p), None if warm is None else warm.ctypes.data_as(C.c_void_p),
-                                    C.c_int(int(warm_shift)))
+                                    C.c_int(int(warm_shift)), None if cost is None else cost.ctypes.data_as(C.c_void_p))
     assert rc == 0
     out["counters"] = counters
     return out

@@ -19,7 +19,7 @@ extern "C" int qp3_host_workspace_bytes(int N, int nn) {
 
 // counters [B,4]: factorisations, solves, active-set rounds, interior-point iterations
 extern "C" int qp3_host_solve_batch(const dmpc_params* p, const dmpc_options* opt, const dmpc_batch_io* io,
-                                    const dmpc_shift_io* sh, int* counters, unsigned char* warm, int warm_shift) {
+                                    const dmpc_shift_io* sh, int* counters, unsigned char* warm, int warm_shift, int* cost) {
   DevParams P;
   memset(&P, 0, sizeof(P));
   fill_dev_params(p, opt, P);
@@ -33,6 +33,9 @@ extern "C" int qp3_host_solve_batch(const dmpc_params* p, const dmpc_options* op
   if (sh) { bp.nx_x0 = sh->x0; bp.nx_xprev = sh->xprev; bp.nx_uprev = sh->uprev; bp.nx_uold = sh->uold; bp.nx_xy = sh->xy_send; bp.hold = sh->hold;
             bp.flags = sh->flags; bp.stop = sh->stop; bp.stop_div = sh->stop_div > 0 ? sh->stop_div : 1; bp.laps = sh->laps; bp.end_s = sh->end_s; }
   bp.warm = warm; bp.warm_shift = warm_shift;
+  std::vector<int> ident(io->B);
+  for (int b = 0; b < io->B; ++b) ident[b] = b;
+  if (cost) { bp.cost = cost; bp.order = ident.data(); }  // previous call's costs: the hard-QP hint is live
   const size_t park = stage_park_doubles(P.N, P.nn);
   std::vector<double> gws((size_t)io->B * park);
   bp.gws = gws.data(); bp.gws_stride = (long long)park;
