@@ -99,6 +99,12 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def stream_capacity(n_qp, A=3):
+    """QPs per iteration the workload generator simulates for n_qp kept QPs (3 % spare platoons)."""
+    S_need = (n_qp + A - 1) // A
+    return (S_need + max(4, S_need // 32)) * A
+
+
 def closed_loop_stream(solve_fn, n_qp, n_batches, cfg, track, N=HORIZON, nn=NN, A=3, topo="full", skip=3, seed0=0):
     """`n_batches` consecutive DMPC iterations of synthetic platoons driven by `solve_fn`, the first `skip` (the cold
     start) dropped; returns the list of input dicts (n_qp QPs per iteration).  A platoon whose experiment the reference
@@ -107,8 +113,8 @@ def closed_loop_stream(solve_fn, n_qp, n_batches, cfg, track, N=HORIZON, nn=NN, 
     is frozen (LPV_HP_N_main.py:102-104) and the first ceil(n_qp/A) platoons that run through the window are kept."""
     from colaborativempc_b200 import scenarios as sc
     S_need = (n_qp + A - 1) // A
-    S = S_need + max(4, S_need // 32)
-    B = S * A
+    B = stream_capacity(n_qp, A)
+    S = B // A
     x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=seed0)
     idx, cnt = sc.topology(A, topo, nn=nn)
     x0 = x0.reshape(B, 9).copy()
@@ -279,7 +285,7 @@ def horizon_sweep(torch, dev, cfg, track, flush, cores, quick):
     for N, B in ((10, 4096), (20, 4096), (50, 4096), (100, 1024)):
         if quick:
             B = min(B, 512)
-        eng = BatchedPlannerLPV(*planner_args(cfg, track, N), nn=NN, max_batch=B + 2)
+        eng = BatchedPlannerLPV(*planner_args(cfg, track, N), nn=NN, max_batch=stream_capacity(B))
         ins = steady_state_inputs(lambda **kw: eng.solve_batch_host(duals=False, **kw), B, cfg, track, N=N)
         d_in = {k: torch.from_numpy(v).to(dev) for k, v in ins.items()}
         d_out = eng.alloc_outputs(B, duals=False)
@@ -318,7 +324,7 @@ def run_single(args):
     W = max(args.warmup, 3)
     nb = W + args.steps
     opts = {"engine": args.engine, "warm_start": 2 if args.warm else 0}
-    mk = lambda o: BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=NN, max_batch=BATCH + 2, options=o)
+    mk = lambda o: BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=NN, max_batch=stream_capacity(BATCH), options=o)
     gen = mk({"engine": args.engine})
     stream = closed_loop_stream(lambda **kw: gen.solve_batch_host(duals=False, **kw), BATCH, nb, cfg, track)
     gen.close()
@@ -378,7 +384,9 @@ def run_single(args):
                    "same stream of batches, measured on the same iterations as `value` (interleaved, own handle)"}
     # ---- the same frozen batch again (previous working sets are exact) and a never-seen batch (nothing carried)
     last = d_in[-1]
-    replay = float(np.mean(_time_calls(torch, lambda: eng.solve_batch(out=d_out, duals=False, **last), 6, flush)[1:]))
+    rep_eng = mk({"engine": args.engine, "warm_start": 1})   # same batch again: the working sets as certified, not shifted
+    rep_eng.solve_batch(out=d_out, duals=False, **last)
+    replay = float(np.mean(_time_calls(torch, lambda: rep_eng.solve_batch(out=d_out, duals=False, **last), 6, flush)[1:]))
     cold_eng = mk({"engine": args.engine, "warm_start": 0, "order_hint": 0})
     cold_eng.solve_batch(out=d_out, duals=False, **last)
     cold = float(np.mean(_time_calls(torch, lambda: cold_eng.solve_batch(out=d_out, duals=False, **last), 5, flush)))
@@ -536,18 +544,16 @@ def run_dmpc(args):
     clocks = sampler.result()
     launches = (eng.launches - launches0) if args.no_graph else args.steps * dm.launches_per_iteration
     stopped = int(dm.stopped().sum())
-    # ---- the solve alone on this rank's current batch (no gather, no exchange), and the collective alone
-    torch.cuda.synchronize()
-    xp = dm.xprev
-    solve_only = lambda: eng.solve_batch(dm.x0, xp, dm.uprev, dm.uold, dm.nbr_xy, dm.pose, dm.nbr_cnt, out=dm.out, duals=False)
-    solve_only()
-    k_ms = float(np.mean(_time_calls(torch, solve_only, 5, flush)))
+    # ---- where a step goes: 8 more closed-loop iterations launched eagerly with CUDA events between the three phases
+    # (gather + stop reduce | solve + bookkeeping + launch order | exchange), and the collective alone on the real buffer
+    ph = np.array([dm.iterate_phases() for _ in range(8)])[2:].mean(0)
+    k_ms = float(ph[1])
     coll = None
     if world > 1:
         coll = float(np.mean(_time_calls(torch, dm.exchange, 50)))
     # ---- reduce over ranks: a step is as slow as its slowest rank
     t = torch.tensor(np.concatenate([ms, walls * 1e3]), dtype=torch.float64, device=dev)
-    cnts = torch.tensor(list(cn) + [k_ms], dtype=torch.float64, device=dev)
+    cnts = torch.tensor(list(cn) + [ph[0], ph[1], ph[2]], dtype=torch.float64, device=dev)
     if world > 1:
         allt = [torch.zeros_like(t) for _ in range(world)]
         dist.all_gather(allt, t)
@@ -566,8 +572,12 @@ def run_dmpc(args):
     if not args.no_config3 and 64 % world == 0:
         config3 = {}
         for name, S3, topo, nn3 in (("chain_1_platoon", 1, "chain", 2), ("chain_64_platoons", 64, "chain", 2), ("full_nn63_8_platoons", 8, "full", 63)):
-            e3, d3 = make(S3, 64, world, rank, topo=topo, nn=nn3, seed0=7)
-            settle(d3, 10)
+            for seed in range(7, 15):   # a single platoon can be one the reference would have stopped: take the first that runs
+                e3, d3 = make(S3, 64, world, rank, topo=topo, nn=nn3, seed0=seed)
+                settle(d3, 10)
+                if S3 > 1 or not d3.stopped().any():
+                    break
+                e3.close()
             _dmpc_loop(torch, d3, 3, None, e2e_io=False)
             barrier()
             m3, _, c3 = _dmpc_loop(torch, d3, 20, None, e2e_io=False)
@@ -600,7 +610,9 @@ def run_dmpc(args):
                 "efficiency_same_workload": (value / (world * weak["value"])) if weak else None,
                 "step_breakdown_ms": {"step_max_over_ranks": float(step_ms.mean()), "rank_step_min": float(dev_ms.mean(1).min()),
                                       "rank_step_median": float(np.median(dev_ms.mean(1))), "rank_step_max": float(dev_ms.mean(1).max()),
-                                      "solve_alone_per_rank": [float(v) for v in allc[:, 7]], "all_gather_alone": coll,
+                                      "eager_phase_gather_per_rank": [float(v) for v in allc[:, 7]],
+                                      "eager_phase_solve_per_rank": [float(v) for v in allc[:, 8]],
+                                      "eager_phase_exchange_per_rank": [float(v) for v in allc[:, 9]], "all_gather_alone": coll,
                                       "all_gather_bytes_per_rank": int(dm.send.numel() * 8),
                                       "wall_minus_device": float(wall_ms.max(0).mean() - step_ms.mean())},
                 "roofline": roofline, "roofline_hbm": roof_hbm, "cpu_baseline": None,

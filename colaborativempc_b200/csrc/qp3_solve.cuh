@@ -20,13 +20,13 @@
 Q3N int polish_round3(int first) {
   Q3_CTX(c);
   Hdr3* hd = c.hd;
-  // Penalty of the rows in the guess.  A soft row (one with a slack) is only ever as stiff as its slack weight: after
-  // the slack elimination its weight is D 2Qs / (2Qs + D) -> 2Qs, so the multiplier iteration contracts by 2Qs / D per
-  // pass on it; it gets 1e3 / delta (hard rows: curvature of the cost, a few 1e2, over 1 / delta).
+  // Penalty of the rows in the guess: 10 / delta.  The multiplier iteration contracts by (curvature seen by the row) / D
+  // per pass, and that curvature is up to 2 Qs = 2e7 for a soft row (after the slack elimination its weight is
+  // D 2Qs / (2Qs + D) -> 2Qs) AND for a hard row whose state is coupled to active soft rows through the dynamics.
 #ifndef Q3_SOFT
 #define Q3_SOFT 10.0
 #endif
-  const double Dv = 1.0 / hd->delta, Ds = Q3_SOFT * Dv, cert_tol = hd->cert_tol;
+  const double Dv = Q3_SOFT / hd->delta, Ds = Dv, cert_tol = hd->cert_tol;
   Q3_FOR(j, c.RT) {
     const bool soft = j < c.Rs && (c.rinfo[j] & 127) != 0;
     c.D[j] = (c.act[j] && row_ok3(c, j)) ? (soft ? Ds : Dv) : 0.0;
@@ -37,6 +37,7 @@ Q3N int polish_round3(int first) {
   factor_solve3(G3_ALM, first);
   primal_step3(c, 1.0);
   int pass = 0;
+  double v_prev = 1e300;
 #pragma unroll 1
   for (;;) {
     eval_residuals3(c);
@@ -62,17 +63,27 @@ Q3N int polish_round3(int first) {
 #endif
     // converged: active rows on their bounds AND the multiplier iteration has stopped moving (the last update is what
     // the multipliers are still off by, times the contraction of a pass)
-    const bool tight = pass >= 1 && v <= 0.1 * cert_tol && (dl <= 1e-7 * lm || pass >= hd->refine);
-    const double tol = tight ? cert_tol : Q3_LOOSE;
+    // pass budget: polish_refine passes, more (up to 3x) while each pass still brings the active rows 8x closer
+    const bool last = pass >= 3 * hd->refine || (pass >= hd->refine && !(v < 0.125 * v_prev));
+    v_prev = v;
+    const bool tight = pass >= 1 && v <= 0.1 * cert_tol && (dl <= 1e-7 * lm || last);
+    // before that, only a CLEARLY wrong guess ends the round early: a pass leaves the active rows lam / D off their
+    // bounds (v), and every other row is off by about as much, so "violated" has to mean well beyond v
+    const double tol = tight ? cert_tol : fmax(Q3_LOOSE, 8.0 * v);
+    // ... and while the active rows are still far from their bounds (multipliers of 1e7 and more leave them 1e-2 off
+    // after the first pass) neither the other rows' residuals nor the multipliers' signs mean anything yet: refine first
+    const bool judge = tight || v <= 1e-4 || last;
     int changed = 0;
-    Q3_FOR(j, c.RT) {
-      if (!row_ok3(c, j)) continue;
-      if (!c.act[j]) { if (c.res[j] > tol * (1.0 + fabs(row_b3(c, j)))) changed = 1; }
-      else if (c.lam[j] < -tol * lm) changed = 1;
+    if (judge) {
+      Q3_FOR(j, c.RT) {
+        if (!row_ok3(c, j)) continue;
+        if (!c.act[j]) { if (c.res[j] > tol * (1.0 + fabs(row_b3(c, j)))) changed = 1; }
+        else if (c.lam[j] < -tol * lm) changed = 1;
+      }
     }
     changed = q3_wor(changed);
     if (tight && !changed) return 1;
-    if (changed || pass >= hd->refine) {
+    if (changed || last) {
       // update the guess with the tight thresholds (a row the loose test let through still moves)
       Q3_FOR(j, c.RT) {
         if (!row_ok3(c, j)) continue;
@@ -101,7 +112,9 @@ Q3D unsigned long long act_hash3(const Ctx3& c) {
 }
 
 // Up to `rounds` rounds; 1 certified, 0 not (cycle or round cap), 2 numerical failure.
-Q3N int pdas3(int rounds, int first) {
+// bail > 0: give up after the first round if it leaves more than `bail` rows in the guess (a cold start whose
+// unconstrained optimum violates that many rows ends in the interior point anyway: do not spend the rounds).
+Q3N int pdas3(int rounds, int first, int bail) {
   Q3_CTX(c);
   int nh = 0;
 #pragma unroll 1
@@ -112,6 +125,11 @@ Q3N int pdas3(int rounds, int first) {
     { int na = 0; for (int j = 0; j < c.RT; ++j) na += c.act[j]; printf("R %d %d %d\n", r, st, na); }
 #endif
     if (st) return st;
+    if (bail > 0 && r == 0) {
+      double na = 0.0;
+      Q3_FOR(j, c.RT) na += c.act[j] ? 1.0 : 0.0;
+      if (q3_wsum(na) > (double)bail) return 0;
+    }
     const unsigned long long h = act_hash3(c);
     int cyc = 0;
     for (int i = 0; i < nh && i < 8; ++i) cyc |= (c.hd->hist[i] == h);
@@ -260,7 +278,13 @@ Q3D int solve_qp3(const Ctx3& c, double* park, const unsigned char* warm, const 
   // first guess: the working set the previous solve of this QP certified (consecutive MPC steps are alike: usually it IS
   // the answer and one round certifies it), else the empty set; the rounds correct a wrong guess either way.  The
   // iterate starts from a bounded (not dynamics-consistent) point; the first solve removes the dynamics defects.
-  Q3_FOR(j, c.RT) c.act[j] = warm ? (warm[j] != 0 && row_ok3(c, j)) : 0;
+  int any_guess = 0;
+  Q3_FOR(j, c.RT) {
+    const int a = warm ? (warm[j] != 0 && row_ok3(c, j)) : 0;
+    c.act[j] = (unsigned char)a;
+    any_guess |= a;
+  }
+  any_guess = q3_wor(any_guess);
   Q3_FOR(j, 9 * c.N) c.x[j] = hd->x0[j % 9];
   Q3_FOR(j, 2 * c.N) c.u[j] = 0.0;
   Q3_FOR(j, 3 * c.N) c.sig[j] = 0.0;
@@ -268,7 +292,7 @@ Q3D int solve_qp3(const Ctx3& c, double* park, const unsigned char* warm, const 
   {
     // budget: 3 pdas_first rounds (as the condensed engine's free rounds); a QP that ended in the interior point last
     // time gets two rounds on its previous working set and then goes there directly
-    const int st = pdas3(hard_hint ? 2 : 3 * hd->pdas_first, 1);
+    const int st = pdas3(hard_hint ? 2 : 3 * hd->pdas_first, 1, any_guess ? 0 : c.N + c.N / 2);
     if (st == 1) return DMPC_SOLVED;
   }
   // the first phase goes two decades below the option: the iterations there cost a tenth of a polish attempt on a wrong guess
@@ -283,7 +307,7 @@ Q3D int solve_qp3(const Ctx3& c, double* park, const unsigned char* warm, const 
     if (rc == 0) { mu_ok = mu_tol; ipm_park3(c, park, 1); }
     Q3_FOR(j, c.RT) c.act[j] = row_ok3(c, j) && (c.lam[j] > c.tt[j]);
     Q3_SYNC();
-    if (pdas3(hd->pdas_after, 0) == 1) return DMPC_SOLVED;
+    if (pdas3(hd->pdas_after, 0, 0) == 1) return DMPC_SOLVED;
     if (rc == 2) break;  // iteration cap: a tighter target from the same start would hit it again
     mu_tol *= 1e-2;
   }

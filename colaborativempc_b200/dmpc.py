@@ -173,6 +173,28 @@ class ShardedDMPC(object):
         self.first = False
         return self.out
 
+    def iterate_phases(self):
+        """One iteration launched eagerly with CUDA events between its phases; returns the device times in ms of
+        (gather + stop reduce, solve + bookkeeping + launch order, exchange).  Synchronises.  For measurements."""
+        torch, e = self.torch, self.eng
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        xp = self.xprev_first if self.first else self.xprev
+        ev[0].record()
+        e.gather_neighbours(self.all, self.nbr_idx, self.nbr_xy, self.pose, self.S, self.A, self.a_local, self.off, stop=self.stop)
+        ev[1].record()
+        if self.fused:
+            e.solve_batch(self.x0, xp, self.uprev, self.uold, self.nbr_xy, self.pose, self.nbr_cnt, out=self.out, duals=False,
+                          shift=self._shift())
+        else:
+            e.solve_batch(self.x0, xp, self.uprev, self.uold, self.nbr_xy, self.pose, self.nbr_cnt, out=self.out, duals=False)
+            e.shift_pack_hold(self.out["z"], self.out["status"], self.x0, self.xprev, self.uprev, self.uold, self.xy_send, self.hold)
+        ev[2].record()
+        self.exchange()
+        ev[3].record()
+        self.first = False
+        torch.cuda.synchronize()
+        return [ev[i].elapsed_time(ev[i + 1]) for i in range(3)]
+
     def scenario_flags(self, s):
         """(ended, failed) of scenario s as of the last exchange, over ALL its agents on all ranks: the reference's loop
         condition (checkEnd, LPV_HP_N_main.py:96) and its break (:102-104).  Host copy of G*A_local doubles; synchronises."""
