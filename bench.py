@@ -572,15 +572,15 @@ def run_dmpc(args):
     if not args.no_config3 and 64 % world == 0:
         config3 = {}
         for name, S3, topo, nn3 in (("chain_1_platoon", 1, "chain", 2), ("chain_64_platoons", 64, "chain", 2), ("full_nn63_8_platoons", 8, "full", 63)):
-            for seed in range(7, 15):   # a single platoon can be one the reference would have stopped: take the first that runs
-                e3, d3 = make(S3, 64, world, rank, topo=topo, nn=nn3, seed0=seed)
+            for seed in range(7, 19):   # a single platoon can be one the reference would have stopped: take the first that
+                e3, d3 = make(S3, 64, world, rank, topo=topo, nn=nn3, seed0=seed)   # runs through the timed window
                 settle(d3, 10)
+                _dmpc_loop(torch, d3, 3, None, e2e_io=False)
+                barrier()
+                m3, _, c3 = _dmpc_loop(torch, d3, 20, None, e2e_io=False)
                 if S3 > 1 or not d3.stopped().any():
                     break
                 e3.close()
-            _dmpc_loop(torch, d3, 3, None, e2e_io=False)
-            barrier()
-            m3, _, c3 = _dmpc_loop(torch, d3, 20, None, e2e_io=False)
             tt = torch.tensor(m3, dtype=torch.float64, device=dev)
             bb = torch.tensor(c3, dtype=torch.float64, device=dev)
             if world > 1:

@@ -25,6 +25,6 @@ for arg in sys.argv[1:]:
     out[key] = {"qps_in_launch": int(qps), "dfma": dfma, "dadd": dadd, "dmul": dmul, "fp64_flops_per_launch": flops,
                 "fp64_flops_per_qp": flops / int(qps),
                 "dram_bytes_per_launch": m.get("dram__bytes_read.sum", 0.0) + m.get("dram__bytes_write.sum", 0.0),
-                "kernel_ms_under_ncu": m.get("gpu__time_duration.sum"), "source": "profiles/" + os.path.basename(path)}
+                "kernel_ns_under_ncu": m.get("gpu__time_duration.sum"), "source": "profiles/" + os.path.basename(path)}
 json.dump(out, open(out_path, "w"), indent=1)
 print(json.dumps(out, indent=1))
