@@ -113,7 +113,7 @@ def default_lib_path():
 
 
 EXPORTS = ["dmpc_default_options", "dmpc_version", "dmpc_create", "dmpc_destroy", "dmpc_last_error",
-           "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_shift_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
+           "dmpc_set_options", "dmpc_solve_batch", "dmpc_solve_batch_static", "dmpc_solve_shift_batch", "dmpc_solve_batch_host", "dmpc_shift_pack",
            "dmpc_shift_pack_hold",
            "dmpc_gather_neighbours", "dmpc_gather_neighbours_stop", "dmpc_launch_count", "dmpc_smem_bytes", "dmpc_engine", "dmpc_sim_batch",
            "dmpc_ocd_lambda_update", "dmpc_ocd_lambda_update_hp"]
@@ -149,6 +149,9 @@ def load_library(path=None):
     lib.dmpc_solve_shift_batch.restype = C.c_int
     lib.dmpc_shift_pack_hold.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 10
     lib.dmpc_shift_pack_hold.restype = C.c_int
+    lib.dmpc_solve_batch_static.argtypes = [C.POINTER(DmpcParams), C.POINTER(DmpcOptions), C.POINTER(DmpcBatchIO), C.c_int32,
+                                            C.c_void_p, C.c_char_p, C.c_int32]
+    lib.dmpc_solve_batch_static.restype = C.c_int
     lib.dmpc_solve_batch_host.argtypes = [C.c_void_p, C.POINTER(DmpcBatchIO)]
     lib.dmpc_solve_batch_host.restype = C.c_int
     lib.dmpc_shift_pack.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 7

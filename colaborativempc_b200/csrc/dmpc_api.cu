@@ -619,3 +619,95 @@ extern "C" int dmpc_gather_neighbours_stop(dmpc_handle* h, int32_t S, int32_t A_
   if (!d_stop) return h ? fail(h, DMPC_ERR_ARG, "dmpc_gather_neighbours_stop needs d_stop%s") : DMPC_ERR_ARG;
   return launch_gather(h, S, A_total, A_local, agent_offset, d_all, d_nbr_idx, d_nbr_xy, d_pose, d_stop, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Allocation-free entry point (no counterpart in the reference).
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
+// the stage-wise solve kernel with its global scratch - the slice of each QP where the interior-point iterate is parked
+// between the phases of the mu ladder - in a file-scope device array instead of a handle-owned cudaMalloc block.
+// The array is held by every GPU that loads this library until the process exits (24 MiB).  All calls share it, and it
+// keeps the last call's contents: the kernel writes a QP's slice before it reads it (ipm_park3 saves before any warm
+// phase loads), so nothing has to start at zero; calls that overlap on the GPU (two streams, two host threads) race on it.
+#define DMPC_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) double dmpc_static_scratch[DMPC_STATIC_SCRATCH_DOUBLES];
+// `dmpc_static_scratch` in HOST code is a stand-in for the symbol, not a device address: the kernel gets the address
+// cudaGetSymbolAddress returns, looked up once per device with that device current.
+static double* g_static_ptr[DMPC_STATIC_MAX_DEVICES];
+static int g_static_optin[DMPC_STATIC_MAX_DEVICES];
+
+static int static_fail(char* err, int32_t err_len, int code, const char* msg, const char* detail = "") {
+  if (err && err_len > 0) snprintf(err, (size_t)err_len, "%s%s", msg, detail);
+  return code;
+}
+
+extern "C" int dmpc_solve_batch_static(const dmpc_params* p, const dmpc_options* opt, const dmpc_batch_io* io, int32_t device,
+                                       void* stream, char* err, int32_t err_len) {
+  if (err && err_len > 0) err[0] = 0;
+  if (!p || !io) return static_fail(err, err_len, DMPC_ERR_ARG, "null params / io");
+  if (io->B == 0) return DMPC_OK;
+  if (p->N < 1 || p->N > 511 || p->nn < 0 || p->nn > 123 || p->nseg < 1 || p->nseg > DMPC_MAX_SEG || !(p->dt > 0) || io->B < 0)
+    return static_fail(err, err_len, DMPC_ERR_ARG, "bad N/nn/nseg/dt/B");
+  if (!psd(p->Q, 9, false) || !psd(p->R, 2, false) || !psd(p->dR, 2, false))
+    return static_fail(err, err_len, DMPC_ERR_ARG, "Q, R and dR must be positive semidefinite");
+  if (!psd(p->Qs, 3, true)) return static_fail(err, err_len, DMPC_ERR_ARG, "Qs must be positive definite");
+  {
+    double rs[4];
+    for (int i = 0; i < 4; ++i) rs[i] = p->R[i] + p->dR[i];
+    if (!psd(rs, 2, true)) return static_fail(err, err_len, DMPC_ERR_ARG, "R + dR must be positive definite (strictly convex inputs)");
+  }
+  dmpc_options o;
+  if (opt) o = *opt; else dmpc_default_options(&o);
+  if (!options_ok(&o)) return static_fail(err, err_len, DMPC_ERR_ARG, "bad options");
+  if (o.engine == DMPC_ENGINE_FAST) return static_fail(err, err_len, DMPC_ERR_UNSUPPORTED, "dmpc_solve_batch_static runs the stage-wise engine only");
+  if (io->xprev_rows < p->N) return static_fail(err, err_len, DMPC_ERR_ARG, "Last_xPredicted needs at least N rows");
+  if (!io->x0 || !io->xprev || !io->uprev || !io->uold || !io->pose || (p->nn > 0 && !io->nbr_xy))
+    return static_fail(err, err_len, DMPC_ERR_ARG, "null input pointer");
+  // the size limit: B QPs x the parked iterate of one QP must fit in the static array
+  const size_t stride = (stage_park_doubles(p->N, p->nn) + 1) & ~(size_t)1;
+  if ((size_t)io->B * stride > (size_t)DMPC_STATIC_SCRATCH_DOUBLES) {
+    char msg[160];
+    snprintf(msg, sizeof(msg), "batch of %d QPs x %zu scratch doubles per QP (N=%d, nn=%d) exceeds the static scratch of %d doubles: at most %zu QPs per call",
+             io->B, stride, p->N, p->nn, (int)DMPC_STATIC_SCRATCH_DOUBLES, (size_t)DMPC_STATIC_SCRATCH_DOUBLES / stride);
+    return static_fail(err, err_len, DMPC_ERR_NOMEM, msg);
+  }
+  cudaError_t e;
+  if (device < 0) { if ((e = cudaGetDevice(&device)) != cudaSuccess) return static_fail(err, err_len, DMPC_ERR_CUDA, "CUDA: ", cudaGetErrorString(e)); }
+  if (device >= DMPC_STATIC_MAX_DEVICES) return static_fail(err, err_len, DMPC_ERR_ARG, "device index beyond DMPC_STATIC_MAX_DEVICES");
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return static_fail(err, err_len, DMPC_ERR_CUDA, "CUDA: ", cudaGetErrorString(e));
+  if (!g_static_ptr[device]) {  // set-up, once per device, that device current (not thread-safe, like the handles)
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return static_fail(err, err_len, DMPC_ERR_CUDA, "CUDA: ", cudaGetErrorString(e));
+    if (prop.major < 10) return static_fail(err, err_len, DMPC_ERR_UNSUPPORTED, "this library is built for sm_100a (B200) only");
+    int optin = 0;
+    if ((e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)) != cudaSuccess)
+      return static_fail(err, err_len, DMPC_ERR_CUDA, "CUDA: ", cudaGetErrorString(e));
+    double* ptr = nullptr;
+    if ((e = cudaGetSymbolAddress((void**)&ptr, dmpc_static_scratch)) != cudaSuccess || !ptr)
+      return static_fail(err, err_len, DMPC_ERR_CUDA, "cudaGetSymbolAddress(dmpc_static_scratch): ", cudaGetErrorString(e));
+    g_static_optin[device] = optin;
+    g_static_ptr[device] = ptr;
+  }
+  Ctx3 c3;
+  const size_t smem = carve_workspace3(c3, nullptr, p->N, p->nn);
+  if (smem + 1024 > (size_t)g_static_optin[device])
+    return static_fail(err, err_len, DMPC_ERR_UNSUPPORTED, "horizon/neighbour count too large for the on-chip workspace");
+  // the opt-in limit is a per-function, per-device setting shared with the handles: always raise it to the device maximum
+  // (never below what a live handle asked for)
+  if ((e = cudaFuncSetAttribute(lpv_qp_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_static_optin[device])) != cudaSuccess)
+    return static_fail(err, err_len, DMPC_ERR_CUDA, "CUDA: ", cudaGetErrorString(e));
+  DevParams P;
+  memset(&P, 0, sizeof(P));
+  fill_dev_params(p, &o, P);
+  BatchPtrs bp;
+  memset(&bp, 0, sizeof(bp));
+  bp.B = io->B; bp.xprev_rows = io->xprev_rows;
+  bp.x0 = io->x0; bp.xprev = io->xprev; bp.uprev = io->uprev; bp.uold = io->uold; bp.nbr_xy = io->nbr_xy; bp.pose = io->pose;
+  bp.nbr_count = io->nbr_count;
+  bp.z = io->z; bp.planes = io->planes; bp.y_ineq = io->y_ineq; bp.y_eq = io->y_eq; bp.obj = io->obj;
+  bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
+  bp.gws = g_static_ptr[device]; bp.gws_stride = (long long)stride;
+  // nothing is carried between calls here: no launch order, no warm start (those live in handle-owned buffers)
+  lpv_qp_stage_kernel<<<io->B, QP3_THREADS, smem, (cudaStream_t)stream>>>(P, bp);
+  if ((e = cudaGetLastError()) != cudaSuccess) return static_fail(err, err_len, DMPC_ERR_CUDA, "CUDA: ", cudaGetErrorString(e));
+  return DMPC_OK;
+}

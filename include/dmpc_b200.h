@@ -239,6 +239,23 @@ int dmpc_ocd_lambda_update(dmpc_handle* h, int32_t S, int32_t A, double alpha, d
 int dmpc_ocd_lambda_update_hp(dmpc_handle* h, int32_t S, int32_t A, double alpha, double dth, const double* d_xy,
                               const double* d_planes, double* d_lambdas, void* stream);
 
+/* Allocation-free variant of dmpc_solve_batch.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Needs no handle: params / options (NULL = defaults) are passed per call, `device` < 0 = current device,
+ * DEVICE buffers in `io`, asynchronous on `stream`.  Stage-wise engine only, nothing carried between calls (no launch
+ * order, no warm start): results are those of a handle with warm_start = 0, order_hint = 0, bit for bit.
+ * The kernel's global scratch (the parked interior-point iterate of each QP) is a static device array of
+ * DMPC_STATIC_SCRATCH_DOUBLES doubles (24 MiB) that every GPU loading the library holds until the process exits:
+ *   io->B * (14 N + 2 N (8 + nn), rounded up to even) doubles must fit - 4626 QPs at N = 20, nn = 2, 925 at N = 100, nn = 2 -
+ * else DMPC_ERR_NOMEM with the limit spelt out in `err` (caller's buffer of err_len bytes, may be NULL).
+ * The call makes no cudaMalloc / cudaFree / allocating library call.  Every call shares the array, which keeps the last
+ * call's contents (the kernel writes a QP's slice before reading it: nothing needs clearing); calls that overlap on the
+ * GPU race on it - keep them stream-ordered.  The first call on a device resolves the array's address
+ * (cudaGetSymbolAddress) and is not thread-safe. */
+#define DMPC_STATIC_SCRATCH_DOUBLES (3 * 1024 * 1024)
+int dmpc_solve_batch_static(const dmpc_params* params, const dmpc_options* opt, const dmpc_batch_io* io, int32_t device,
+                            void* stream, char* err, int32_t err_len);
+
 /* Engine the handle runs on: DMPC_ENGINE_STAGE or DMPC_ENGINE_FAST (what DMPC_ENGINE_AUTO resolved to). */
 int dmpc_engine(const dmpc_handle* h);
 
