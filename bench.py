@@ -499,6 +499,8 @@ def run_dmpc(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    made = []   # every ShardedDMPC of this run: their graphs are released before the process group is torn down
+
     def make(S, A, w, r, topo="chain", nn=NN, seed0=0):
         eng = BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=nn, max_batch=S * A // w, options=opts)
         x0, xprev, uprev = sc.platoon_scenarios(S, A, HORIZON, cfg["dt"], track, seed0=seed0)
@@ -506,6 +508,7 @@ def run_dmpc(args):
         dm = ShardedDMPC(eng, S, A, idx, cnt, x0, xprev, uprev, rank=r, world=w, end_s=1e9)  # synthetic run: no end of track
         if not args.warm:
             eng.set_options(warm_start=0)
+        made.append(dm)
         return eng, dm
 
     def settle(dm, n):
@@ -628,13 +631,26 @@ def run_dmpc(args):
                 "ipm_iters_mean": float(allc[:, 5].sum()) / max(qp_timed, 1), "polish_rounds_mean": float(allc[:, 6].sum()) / max(qp_timed, 1),
                 "config3": config3}
         print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
-    # a QP that is genuinely infeasible stops its scenario (reported above); a numerical breakdown fails the run, and so
-    # does a run in which more than 1 % of the timed QPs were not feasible
-    if breakdowns or not_feasible > 0.01 * qp_timed:
+    rc = 3 if (breakdowns or not_feasible > 0.01 * qp_timed) else 0
+    if rc:
         sys.stderr.write("FAIL: %d breakdowns, %d of %d timed QPs not feasible\n" % (breakdowns, not_feasible, int(qp_timed)))
-        sys.exit(3)
+    if world > 1:
+        # captured graphs hold NCCL work: drop them first, then tear the group down with a hard limit (the result line is
+        # out; a teardown that does not come back must not keep the job alive)
+        for m in made:
+            m.release()
+        import gc
+        gc.collect()
+        barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        t = threading.Thread(target=dist.destroy_process_group, daemon=True)
+        t.start()
+        t.join(20.0)
+        if t.is_alive():
+            os._exit(rc)
+    sys.exit(rc)   # a genuinely infeasible QP stops its scenario (reported above); a numerical breakdown, or more than
+                   # 1 % of the timed QPs not feasible, fails the run
 
 
 def main():
@@ -654,6 +670,9 @@ def main():
     ap.add_argument("--workload", default="batch", choices=["batch", "dmpc"],
                     help="N=1 only: 'dmpc' runs the multi-GPU step (16-agent platoons, closed loop) on one GPU")
     args = ap.parse_args()
+    if os.environ.get("DMPC_BENCH_WATCHDOG"):   # development: dump every thread's stack if the run is still going after N s
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["DMPC_BENCH_WATCHDOG"]), exit=True)
     if args.impl == "reference":
         run_reference(args)
     elif int(os.environ.get("WORLD_SIZE", "1")) == 1 and args.workload == "batch":

@@ -164,6 +164,12 @@ class ShardedDMPC(object):
         self.graph = g
         return g
 
+    def release(self):
+        """Drops the captured graph (it holds NCCL work: release it BEFORE torch.distributed.destroy_process_group, which
+        otherwise waits forever on the communicator the graph still references).  Synchronises."""
+        self.graph = None
+        self.torch.cuda.synchronize()
+
     def iterate(self):
         """One DMPC iteration; asynchronous on the current stream.  Returns the output dict of the solve."""
         if self.graph is not None:
