@@ -176,6 +176,105 @@ def test_closed_loop_vs_oracle(built, cfg, track, Nh, nn, topo, S, A, iters):
     assert n_cmp > 0
 
 
+def _compare_certified(cfg, track, ins, out, Nh, nn, rows=None, min_ok=0.9):
+    """Oracle (exact mode) on `rows` of a batch: every QP it certifies must be certified here and equal at 1e-6 with the same
+    active set; returns the number compared."""
+    rows = np.arange(ins["x0"].shape[0]) if rows is None else np.asarray(rows)
+    sub = {k: (None if v is None else np.ascontiguousarray(v[rows])) for k, v in ins.items()}
+    o = _oracle(cfg, track, sub, N=Nh, nn=nn)
+    ok = o["status"] == 1
+    assert ok.mean() >= min_ok, ok.mean()
+    got = {k: v[rows][ok] for k, v in out.items()}
+    _compare(got, o["z"][ok], o["y"][ok], o["obj"][ok], o["planes"][ok], (8 + nn) * Nh)
+    return int(ok.sum())
+
+
+def test_bench_workload_sample_vs_oracle(built, cfg, track):
+    """BASELINE config[1] exactly as bench.py builds it (same generator, same seeds): 256 evenly spaced QPs of the first
+    TIMED batch (closed-loop iteration 6 of the 1 366 platoons) against the oracle; the whole batch certified."""
+    import bench
+    eng = _engine(cfg, track, max_batch=bench.stream_capacity(bench.BATCH))
+    stream = bench.closed_loop_stream(lambda **kw: eng.solve_batch_host(duals=False, **kw), bench.BATCH, 4, cfg, track)
+    ins = stream[3]
+    assert ins["x0"].shape[0] == 4096
+    out = eng.solve_batch_host(**ins)
+    assert np.all(out["status"] == 1), np.unique(out["status"], return_counts=True)
+    assert _compare_certified(cfg, track, ins, out, N, 2, rows=np.arange(0, 4096, 16)) >= 250
+
+
+@pytest.mark.parametrize("A,topo,nn,S,its", [(16, "chain", 2, 8, (0, 3, 40)), (64, "chain", 2, 2, (0, 3, 40)),
+                                             (64, "full", 63, 1, (0, 3)), (16, "full", 15, 2, (0, 3, 12))])
+def test_platoon_configs_vs_oracle(built, cfg, track, A, topo, nn, S, its):
+    """BASELINE configs 3 and 5: the 16-agent chain the multi-GPU bench times, the 64-vehicle platoon as a chain and fully
+    connected (nn = 63), 16 agents fully connected - closed loop on the device (`ShardedDMPC`, warm start and launch
+    order live), the batches of iterations `its` re-solved by the oracle."""
+    import torch
+    from colaborativempc_b200 import scenarios as sc
+    from colaborativempc_b200.dmpc import ShardedDMPC
+    x0, xprev, uprev = sc.platoon_scenarios(S, A, N, cfg["dt"], track, seed0=8)
+    idx, cnt = sc.topology(A, topo, nn=nn)
+    eng = _engine(cfg, track, nn=nn, max_batch=S * A)
+    dm = ShardedDMPC(eng, S, A, idx, cnt, x0, xprev, uprev, end_s=1e9)
+    dm.out = eng.alloc_outputs(dm.B, duals=True)
+    n_cmp = 0
+    for it in range(max(its) + 1):
+        keep = it in its
+        if keep:
+            ins = dict(x0=dm.x0.cpu().numpy(), xprev=(dm.xprev_first if dm.first else dm.xprev).cpu().numpy(),
+                       uprev=dm.uprev.cpu().numpy(), uold=dm.uold.cpu().numpy(), nbr_count=dm.nbr_cnt.cpu().numpy())
+        e = dm.eng   # the body of ShardedDMPC.iterate with the duals switched on
+        e.gather_neighbours(dm.all, dm.nbr_idx, dm.nbr_xy, dm.pose, dm.S, dm.A, dm.a_local, dm.off, stop=dm.stop)
+        e.solve_batch(dm.x0, dm.xprev_first if dm.first else dm.xprev, dm.uprev, dm.uold, dm.nbr_xy, dm.pose, dm.nbr_cnt,
+                      out=dm.out, duals=True, shift=dm._shift())
+        dm.first = False
+        dm.exchange()
+        torch.cuda.synchronize()
+        st = dm.out["status"].cpu().numpy()
+        run = ~np.repeat(dm.stop.cpu().numpy().astype(bool), A)
+        assert not np.isin(st[run], (-10, -20, -21)).any()
+        if keep:
+            ins.update(nbr_xy=dm.nbr_xy.cpu().numpy(), pose=dm.pose.cpu().numpy())
+            out = {k: v.cpu().numpy() for k, v in dm.out.items()}
+            rows = np.flatnonzero(run & (st == 1))
+            assert rows.size >= 0.95 * run.sum()
+            n_cmp += _compare_certified(cfg, track, ins, out, N, nn, rows=rows, min_ok=0.85)
+    assert n_cmp >= 0.8 * len(its) * S * A
+
+
+def test_config1_closed_loop_to_check_end(built, cfg, track):
+    """BASELINE config 1: the reference's own experiment (planner/scripts/LPV_HP_N_main.py:57-122) at N = 20 - the three
+    vehicles of x0_database[0:3], fully connected, from the reference's cold start, driven through the drop-in path until
+    checkEnd (utilities/misc.py:28-48) fires - with EVERY iteration's three QPs re-solved by the oracle."""
+    from colaborativempc_b200 import scenarios as sc
+    from colaborativempc_b200.runlog import check_end
+    eng = _engine(cfg, track, max_batch=3, options={"warm_start": 2})
+    agents, xs, us = sc.initialise_agents(sc.X0_DATABASE[0:3], N, cfg["dt"], track)
+    idx, cnt = sc.topology(3, "full", nn=2)
+    L = float(np.ravel(track.TrackLength)[0])
+    x0 = np.stack([x[0] for x in xs])
+    xprev, uprev, uold = np.stack(xs), np.stack(us), np.zeros((3, 2))
+    xy = xprev[None, :, :, 7:9].copy()
+    rec, s_now, it = [], x0[None, :, 6], 0
+    while it < 2000 and not check_end(s_now, L)[0]:
+        nbr, pose = sc.gather_neighbours(xy, idx)
+        ins = dict(x0=x0, xprev=xprev, uprev=uprev, uold=uold, nbr_xy=nbr.reshape(3, N + 1, 2, 2), pose=pose.reshape(3, N + 1, 2),
+                   nbr_count=np.asarray(cnt, np.int32))
+        out = eng.solve_batch_host(**ins)
+        assert np.all(np.isin(out["status"], (1, 2))), (it, out["status"])     # feasible throughout, as in the recorded runs
+        rec.append((ins, out))
+        x0, xprev, uprev, uold, xyb = sc.dmpc_shift(out["z"], N)
+        xy = xyb[None]
+        s_now = out["z"][:, :12 * (N + 1)].reshape(3, N + 1, 12)[None, :, 0, 6]
+        it += 1
+    assert 200 < it < 2000 and check_end(s_now, L)[0]          # the run ENDED at the end of the track (47 m at ~3 m/s)
+    n = _compare_certified(cfg, track, rec[0][0], rec[0][1], N, 2, min_ok=1.0)   # first call: N + 1 history rows
+    big_in = {k: np.concatenate([r[0][k] for r in rec[1:]], 0) for k in INPUT_KEYS}
+    big_out = {k: np.concatenate([r[1][k] for r in rec[1:]], 0) for k in rec[0][1]}
+    assert (big_out["status"] == 1).mean() > 0.99
+    n += _compare_certified(cfg, track, big_in, big_out, N, 2, rows=np.flatnonzero(big_out["status"] == 1), min_ok=0.97)
+    assert n > 0.97 * 3 * it
+
+
 def test_device_and_host_entry_points_agree(built, cfg, track):
     import torch
     fx = golden("platoon_N20.npz")
