@@ -81,6 +81,7 @@ struct Hdr3 {
   int refine, pdas_first, pdas_after, ipm_max;
   int n_rounds, n_ipm, n_fact, n_solve;
   double delta, cert_tol, ipm_mu0;
+  double ipm_al;      // length of the interior point's last step (0: none taken yet), for the Tapia indicators
   double Qs2[9];      // 2 Qs
   double R2[4], dR2[4];
   double q0;          // 2 * (-vx_ref Q[0,0])   (LPV_Planner.py:412)

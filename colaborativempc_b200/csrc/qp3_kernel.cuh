@@ -18,7 +18,7 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
       hd->N = N; hd->nn = nn; hd->cnt = cnt < 0 ? 0 : (cnt > nn ? nn : cnt); hd->rows = io.xprev_rows;
       hd->refine = P.refine; hd->pdas_first = P.pdas_first; hd->pdas_after = P.pdas_after; hd->ipm_max = P.ipm_max;
       hd->n_rounds = 0; hd->n_ipm = 0; hd->n_fact = 0; hd->n_solve = 0;
-      hd->delta = P.delta; hd->cert_tol = P.cert_tol; hd->ipm_mu0 = P.ipm_mu0;
+      hd->delta = P.delta; hd->cert_tol = P.cert_tol; hd->ipm_mu0 = P.ipm_mu0; hd->ipm_al = 0.0;
       hd->q0 = 2.0 * (-P.vx_ref * P.Q00);
       hd->lim[0] = P.min_vel; hd->lim[1] = P.max_vel; hd->lim[2] = P.max_rs; hd->lim[3] = P.max_ls;
       hd->lim[4] = P.max_ac; hd->lim[5] = P.max_dc; hd->mind = P.min_dist;

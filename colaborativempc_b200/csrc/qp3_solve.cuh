@@ -64,7 +64,10 @@ Q3N int polish_round3(int first) {
     // converged: active rows on their bounds AND the multiplier iteration has stopped moving (the last update is what
     // the multipliers are still off by, times the contraction of a pass)
     // pass budget: polish_refine passes, more (up to 3x) while each pass still brings the active rows 8x closer
-    const bool last = pass >= 3 * hd->refine || (pass >= hd->refine && !(v < 0.125 * v_prev));
+    // a pass that does not even halve a violation of 1e-3 and more: the rows of the guess cannot all be met (an
+    // inconsistent guess keeps v where it is while the multipliers grow without bound) - do not refine it
+    const bool stuck = pass >= 1 && v > 1e-3 && !(v < 0.5 * v_prev);
+    const bool last = stuck || pass >= 3 * hd->refine || (pass >= hd->refine && !(v < 0.125 * v_prev));
     v_prev = v;
     const bool tight = pass >= 1 && v <= 0.1 * cert_tol && (dl <= 1e-7 * lm || last);
     // before that, only a CLEARLY wrong guess ends the round early: a pass leaves the active rows lam / D off their
@@ -112,9 +115,10 @@ Q3D unsigned long long act_hash3(const Ctx3& c) {
 }
 
 // Up to `rounds` rounds; 1 certified, 0 not (cycle or round cap), 2 numerical failure.
-// bail > 0: give up after the first round if it leaves more than `bail` rows in the guess (a cold start whose
-// unconstrained optimum violates that many rows ends in the interior point anyway: do not spend the rounds).
-Q3N int pdas3(int rounds, int first, int bail) {
+// bail > 0: give up after any round from `bail_from` on that leaves more than `bail` rows in the guess (a QP whose
+// guesses hold that many rows ends in the interior point anyway: do not spend the rounds; a warm first guess may
+// legitimately be that large, so for it the test starts after the second round).
+Q3N int pdas3(int rounds, int first, int bail, int bail_from) {
   Q3_CTX(c);
   int nh = 0;
 #pragma unroll 1
@@ -125,7 +129,7 @@ Q3N int pdas3(int rounds, int first, int bail) {
     { int na = 0; for (int j = 0; j < c.RT; ++j) na += c.act[j]; printf("R %d %d %d\n", r, st, na); }
 #endif
     if (st) return st;
-    if (bail > 0 && r == 0) {
+    if (bail > 0 && r >= bail_from) {
       double na = 0.0;
       Q3_FOR(j, c.RT) na += c.act[j] ? 1.0 : 0.0;
       if (q3_wsum(na) > (double)bail) return 0;
@@ -268,8 +272,30 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     }
     Q3_SYNC();
     lin *= 1.0 - al;
+    if (Q3_LANE == 0) hd->ipm_al = al;
+    Q3_SYNC();
   }
   return 2;
+}
+
+// Working-set guess from the interior-point iterate.  Tapia indicators (the ratios of successive iterates: lam+/lam -> 1
+// and t+/t -> 0 on an active row, the other way round on an inactive one) are scale-free, unlike lam > t: a row that is
+// nearly active (t ~ 1e-6) next to multipliers of 1e7 is told apart decades of mu earlier.  Ends with a barrier.
+Q3D void ipm_guess3(const Ctx3& c) {
+  const double al = c.hd->ipm_al;
+  Q3_FOR(j, c.RT) {
+    int a = 0;
+    if (row_ok3(c, j)) {
+      if (al > 0.0) {
+        const double l0 = c.lam[j] - al * c.dlam[j], t0 = c.tt[j] - al * c.dtt[j];
+        a = (l0 > 0.0 && t0 > 0.0) ? (c.lam[j] * t0 > c.tt[j] * l0) : (c.lam[j] > c.tt[j]);
+      } else {
+        a = c.lam[j] > c.tt[j];
+      }
+    }
+    c.act[j] = (unsigned char)a;
+  }
+  Q3_SYNC();
 }
 
 // Full solve.  Returns dmpc_status; the header counts the work done.  `park`: the QP's global scratch slice.
@@ -291,12 +317,11 @@ Q3D int solve_qp3(const Ctx3& c, double* park, const unsigned char* warm, const 
   Q3_SYNC();
   {
     // budget: 3 pdas_first rounds (as the condensed engine's free rounds); a QP that ended in the interior point last
-    // time gets two rounds on its previous working set and then goes there directly
-    const int st = pdas3(hard_hint ? 2 : 3 * hd->pdas_first, 1, any_guess ? 0 : c.N + c.N / 2);
+    // time gets one round on its previous working set and then goes there directly (95 % of them end there again)
+        const int st = pdas3(hard_hint ? 1 : 3 * hd->pdas_first, 1, c.N + c.N / 2, any_guess ? 1 : 0);
     if (st == 1) return DMPC_SOLVED;
   }
-  // the first phase goes two decades below the option: the iterations there cost a tenth of a polish attempt on a wrong guess
-  double mu_tol = 1e-2 * hd->ipm_mu0, mu_ok = 0.0;
+  double mu_tol = hd->ipm_mu0, mu_ok = 0.0;
 #pragma unroll 1
   while (mu_tol > 1e-13) {
     const int rc = ipm3(mu_tol, mu_ok > 0.0, park);
@@ -305,9 +330,8 @@ Q3D int solve_qp3(const Ctx3& c, double* park, const unsigned char* warm, const 
       break;
     }
     if (rc == 0) { mu_ok = mu_tol; ipm_park3(c, park, 1); }
-    Q3_FOR(j, c.RT) c.act[j] = row_ok3(c, j) && (c.lam[j] > c.tt[j]);
-    Q3_SYNC();
-    if (pdas3(hd->pdas_after, 0, 0) == 1) return DMPC_SOLVED;
+    ipm_guess3(c);
+    if (pdas3(hd->pdas_after, 0, 0, 0) == 1) return DMPC_SOLVED;
     if (rc == 2) break;  // iteration cap: a tighter target from the same start would hit it again
     mu_tol *= 1e-2;
   }
