@@ -37,6 +37,7 @@ static inline double q3_wmax(double v) { return v; }
 static inline double q3_wmin(double v) { return v; }
 static inline int q3_wor(int v) { return v; }
 static inline unsigned long long q3_wsum64(unsigned long long v) { return v; }
+static inline double q3_rcp(double d) { return 1.0 / d; }
 static thread_local char* q3_host_smem = nullptr;
 #define Q3_SMEM q3_host_smem
 #else
@@ -68,6 +69,22 @@ __device__ __forceinline__ unsigned long long q3_wsum64(unsigned long long v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// 1 / d without the slow-path branch of the division: d = m 2^e, single-precision seed for 1 / m, three Newton steps (the
+// last in residual form: relative error about one ulp), exponent put back by integer arithmetic - safe over the whole
+// range a 2 x 2 determinant with interior-point weights lam / t can take (1e38 and beyond).  Non-finite or zero d gives NaN.
+__device__ __forceinline__ double q3_rcp(double d) {
+  const int hi = __double2hiint(d), lo = __double2loint(d);
+  const int e = (hi >> 20) & 0x7ff;
+  const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, lo);  // [1, 2)
+  double x = (double)__frcp_rn((float)m);
+  x = x * fma(-m, x, 2.0);
+  x = x * fma(-m, x, 2.0);
+  x = fma(x, fma(-m, x, 1.0), x);
+  const int xh = (__double2hiint(x) - ((e - 1023) << 20)) | (hi & 0x80000000);
+  const double res = __hiloint2double(xh, __double2loint(x));
+  return (e == 0 || e == 0x7ff) ? __longlong_as_double(0x7ff8000000000000LL) : res;
+}
+
 extern __shared__ __align__(16) char smem_stage[];
 #define Q3_SMEM smem_stage
 #endif
@@ -91,7 +108,8 @@ struct Hdr3 {
   int nq;                   // nonzeros of the upper triangle of 2 Q (P = 2 blockdiag(...), LPV_Planner.py:399-410)
   double Q2u[45];           // 2 Q at the 45 upper-triangle pairs (tri order)
   // cost-to-go and the per-stage temporaries of the Riccati passes (layout: see ric_factor_backward3)
-  double Pf[99];            // [Pxx (9 x 9); Pvx (2 x 9)], row stride 9 (bank-conflict free for one row per lane pair)
+  alignas(16) double Pf[99];  // [Pxx (9 x 9); Pvx (2 x 9)], row stride 9 (bank-conflict free for one row per lane pair)
+                            // (device: Pf .. dbuf, 248 doubles, double as the 2 x 88 exchange buffer of ric_factor_backward3)
   double Pvv[4], px[2][9], pv[2][2], pe[9];
   double Y[44], Yb[22];     // Pf [Acol | d] (11 x 4),  Pf [b0 | b1] (11 x 2)
   double TA[9], Apx[3], Fc[18];
@@ -117,6 +135,7 @@ struct Ctx3 {
 };
 
 #define Q3_HDR_BYTES ((sizeof(Hdr3) + 15) & ~(size_t)15)
+#define Q3_AS 28  // doubles per stage of Acol (27 used): keeps every stage's block 16-byte aligned for 128-bit loads
 
 // doubles per QP after the header
 Q3HD size_t carve_workspace3(Ctx3& c, char* sm, int N, int nn) {
@@ -125,7 +144,7 @@ Q3HD size_t carve_workspace3(Ctx3& c, char* sm, int N, int nn) {
   double* p = (double*)(sm + Q3_HDR_BYTES);
   auto take = [&](size_t n) { double* r = p; p += n; return r; };
   const size_t n = (size_t)N, RT = (size_t)c.RT;
-  c.Acol = take(27 * n); c.Bcol = take(4 * n);
+  c.Acol = take(Q3_AS * n); c.Bcol = take(4 * n);
   c.ax = take(n * nn); c.ay = take(n * nn); c.mx = take(n * nn); c.my = take(n * nn);
   c.eyb = take(n); c.pxy = take(2 * n);
   c.x = take(9 * n); c.u = take(2 * n); c.sig = take(3 * n); c.lam = take(RT); c.tt = take(RT);
@@ -339,7 +358,7 @@ Q3D int setup_linearise3(const Ctx3& c, const DevParams& P, const double* xprev,
                            ce / den, -se / den, 0.0,
                            ct, -st, 0.0,
                            st, ct, 0.0};
-    double* A = c.Acol + 27 * k;
+    double* A = c.Acol + Q3_AS * k;
     for (int r = 0; r < 9; ++r)
       for (int j = 0; j < 3; ++j) A[r * 3 + j] = (r == j ? 1.0 : 0.0) + P.dt * Ac[r * 3 + j];
     double* B = c.Bcol + 4 * k;
@@ -477,16 +496,42 @@ Q3D void assemble_gradient3(const Ctx3& c, int mode, double smu) {
 // dynamics defect of stage k at the current iterate, component j:  (A_k x_k + B_k u_k - x_{k+1})_j
 Q3D double defect3(const Ctx3& c, int k, int j) {
   const double* xk = k > 0 ? c.x + 9 * (k - 1) : c.hd->x0;
-  return arow3(c.Acol + 27 * k, xk, j) + brow3(c.Bcol + 4 * k, c.u[2 * k], c.u[2 * k + 1], j) - c.x[9 * k + j];
+  return arow3(c.Acol + Q3_AS * k, xk, j) + brow3(c.Bcol + 4 * k, c.u[2 * k], c.u[2 * k + 1], j) - c.x[9 * k + j];
 }
 
-// one work item on the device = the lane with that index; on the host every item runs
+// The dynamics defects of every stage at the current iterate, into the scratch c.dlam (9N <= 2 RT doubles over dlam, dtt:
+// free whenever a solve runs with defects - the bounded starting point of the rounds and of the interior point).
+// Ends with a barrier.
+Q3D void stage_defects3(const Ctx3& c) {
+  Q3_FOR(i, 9 * c.N) { const int k = i / 9; c.dlam[i] = defect3(c, k, i - 9 * k); }
+  Q3_SYNC();
+}
+
+// One work item per lane.  On the device a phase is STRAIGHT-LINE code: every lane runs every item group's body on a
+// clamped index and only the stores are predicated (l_ok) - a divergent region per group costs this latency-bound warp a
+// reconvergence bubble each and keeps the compiler from interleaving the groups' dependent chains.  On the host (one
+// "lane") the same bodies run as loops over the items.
 #ifdef QP3_HOST
 #define Q3_ITEM(l, n) for (int l = 0; l < (n); ++l)
 #define Q3_ITEMS(l, lo, hi) for (int l = (lo); l < (hi); ++l)
+#define Q3_PRED(l, n) for (int l = 0; l < (n); ++l) if (const bool l##_ok = true; true)
+#define Q3_PREDS(l, lo, hi) for (int l = (lo); l < (hi); ++l) if (const bool l##_ok = true; true)
+#define Q3_PRED2(l, n) for (int l = 0; l < (n); ++l) if (const bool l##_ok = true; true) if (const int l##_p = 0; true)
+#define Q3_LOCAL_N(n) (n)              // per-lane copies of a table: the host keeps all n entries
+#define Q3_LOCAL_E(q) (q)              // entry q of the per-lane copy = item q
+#define Q3_LOCAL_AT(arr, l) arr[l]
 #else
 #define Q3_ITEM(l, n) for (int l = Q3_LANE; l < (n); l += 32)
 #define Q3_ITEMS(l, lo, hi) for (int l = Q3_LANE; l >= (lo) && l < (hi); l += 32)
+#define Q3_PRED(l, n) if (const bool l##_ok = Q3_LANE < (n); true) if (const int l = l##_ok ? Q3_LANE : (n) - 1; true)
+#define Q3_PREDS(l, lo, hi) if (const bool l##_ok = Q3_LANE >= (lo) && Q3_LANE < (hi); true) if (const int l = l##_ok ? Q3_LANE : (lo); true)
+#define Q3_PRED2(l, n)                                                            \
+  _Pragma("unroll") for (int l##_p = 0; l##_p < 2; ++l##_p)                        \
+    if (const bool l##_ok = Q3_LANE + 32 * l##_p < (n); true)                      \
+      if (const int l = l##_ok ? Q3_LANE + 32 * l##_p : (n) - 1; true)
+#define Q3_LOCAL_N(n) 2                // a lane keeps the entries of its (at most two) items
+#define Q3_LOCAL_E(q) (Q3_LANE + 32 * (q) < 45 ? Q3_LANE + 32 * (q) : 44)
+#define Q3_LOCAL_AT(arr, l) arr[l##_p]
 #endif
 
 // ---------------------------------------------------------------------------------------------------
@@ -513,6 +558,13 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
   double* px = hd->px[0];
   double* pv = hd->pv[0];
   const double* dR2 = hd->dR2;
+  // the triangle tables of this lane's entries, out of the stage loop (the loop's stores could alias the byte tables)
+  int t_i[Q3_LOCAL_N(45)], t_j[Q3_LOCAL_N(45)], t_w[Q3_LOCAL_N(45)];
+  double t_q[Q3_LOCAL_N(45)];
+  for (int q = 0; q < Q3_LOCAL_N(45); ++q) {
+    const int e = Q3_LOCAL_E(q), ij = hd->tri[e];
+    t_i[q] = ij >> 4; t_j[q] = ij & 15; t_w[q] = hd->wix[e] != 255 ? hd->wix[e] : -1; t_q[q] = hd->Q2u[e];
+  }
   Q3_ITEM(e, 45) {
     const int ij = hd->tri[e], i = ij >> 4, j = ij & 15;
     const double v = qt3(c, N - 1, e);
@@ -520,16 +572,17 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
   }
   Q3_ITEM(e, 18) Pf[81 + e] = 0.0;
   Q3_ITEM(e, 4) hd->Pvv[e] = 0.0;
-  Q3_ITEM(e, 9) { px[e] = c.gx[9 * (N - 1) + e]; hd->dbuf[(N - 1) & 1][e] = defects ? defect3(c, N - 1, e) : 0.0; hd->dbuf[N & 1][e] = 0.0; }
+  Q3_ITEM(e, 9) { px[e] = c.gx[9 * (N - 1) + e]; hd->dbuf[(N - 1) & 1][e] = defects ? c.dlam[9 * (N - 1) + e] : 0.0; hd->dbuf[N & 1][e] = 0.0; }
   Q3_ITEM(e, 2) pv[e] = 0.0;
   Q3_SYNC();
 #pragma unroll 1
   for (int k = N - 1; k >= 0; --k) {
-    const double* A = c.Acol + 27 * k;
+    const double* A = c.Acol + Q3_AS * k;
     const double* B = c.Bcol + 4 * k;
     const double* d = hd->dbuf[k & 1];
+    const double B0 = B[0], B1 = B[1], B2 = B[2], B3 = B[3];
     // ---- phase 1
-    Q3_ITEM(l, 22) {
+    Q3_PRED(l, 22) {
       const int r = l >> 1, h = l & 1;
       double p[9];
 #pragma unroll
@@ -545,25 +598,29 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
       }
       a0 = fma(p[8], z0p[24], a0) + a1;
       b0 = fma(p[8], z1p[st1 * 8], b0) + b1;
-      hd->Y[r * 4 + 2 * h] = a0;
-      hd->Y[r * 4 + 2 * h + 1] = b0;
-      hd->Yb[r * 2 + h] = h ? B[3] * p[0] : fma(B[0], p[0], fma(B[1], p[1], B[2] * p[2]));
-      if (h && r < 9) hd->pe[r] = px[r] + b0;
+      const double yb = h ? B3 * p[0] : fma(B0, p[0], fma(B1, p[1], B2 * p[2]));
+      const double pxe = px[r < 9 ? r : 0] + b0;
+      if (l_ok) {
+        hd->Y[r * 4 + 2 * h] = a0;
+        hd->Y[r * 4 + 2 * h + 1] = b0;
+        hd->Yb[r * 2 + h] = yb;
+        if (h && r < 9) hd->pe[r] = pxe;
+      }
     }
     Q3_SYNC();
     // ---- phase 2: scalar section, identical on every lane
     const double* Yb = hd->Yb;
     const double* db = c.D + c.Rs + 4 * k;
     const double pe0 = hd->pe[0], pe1 = hd->pe[1], pe2 = hd->pe[2];
-    const double hu0 = c.gu[2 * k] + pv[0] + hd->Y[39] + fma(B[0], pe0, fma(B[1], pe1, B[2] * pe2));
-    const double hu1 = c.gu[2 * k + 1] + pv[1] + hd->Y[43] + B[3] * pe0;
-    const double H00 = hd->R2[0] + db[0] + db[1] + dR2[0] + fma(B[0], Yb[0], fma(B[1], Yb[2], B[2] * Yb[4])) + 2.0 * Yb[18] + hd->Pvv[0];
-    const double H01 = hd->R2[1] + dR2[1] + fma(B[0], Yb[1], fma(B[1], Yb[3], B[2] * Yb[5])) + Yb[19] + Yb[20] + hd->Pvv[1];
-    const double H11 = hd->R2[3] + db[2] + db[3] + dR2[3] + B[3] * Yb[1] + 2.0 * Yb[21] + hd->Pvv[3];
-    const double idet = 1.0 / (H00 * H11 - H01 * H01);
+    const double hu0 = c.gu[2 * k] + pv[0] + hd->Y[39] + fma(B0, pe0, fma(B1, pe1, B2 * pe2));
+    const double hu1 = c.gu[2 * k + 1] + pv[1] + hd->Y[43] + B3 * pe0;
+    const double H00 = hd->R2[0] + db[0] + db[1] + dR2[0] + fma(B0, Yb[0], fma(B1, Yb[2], B2 * Yb[4])) + 2.0 * Yb[18] + hd->Pvv[0];
+    const double H01 = hd->R2[1] + dR2[1] + fma(B0, Yb[1], fma(B1, Yb[3], B2 * Yb[5])) + Yb[19] + Yb[20] + hd->Pvv[1];
+    const double H11 = hd->R2[3] + db[2] + db[3] + dR2[3] + B3 * Yb[1] + 2.0 * Yb[21] + hd->Pvv[3];
+    const double idet = q3_rcp(H00 * H11 - H01 * H01);
     const double W00 = H11 * idet, W01 = -H01 * idet, W11 = H00 * idet;
     const double z0 = W00 * hu0 + W01 * hu1, z1 = W01 * hu0 + W11 * hu1;
-    Q3_ITEM(l, 12) {
+    Q3_PRED(l, 12) {
       const int col = l < 9 ? l / 3 : l - 9;
       const double* v = l < 9 ? hd->Y + (l % 3) : hd->pe;
       const int sv = l < 9 ? 4 : 1;
@@ -571,43 +628,49 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
 #pragma unroll
       for (int q = 0; q < 8; q += 2) { a0 = fma(A[3 * q + col], v[sv * q], a0); a1 = fma(A[3 * q + 3 + col], v[sv * (q + 1)], a1); }
       a0 = fma(A[24 + col], v[sv * 8], a0) + a1;
-      if (l < 9) hd->TA[l] = a0; else hd->Apx[l - 9] = a0;
+      if (l_ok) { if (l < 9) hd->TA[l] = a0; else hd->Apx[l - 9] = a0; }
     }
-    Q3_ITEMS(l, 12, 30) {
+    Q3_PREDS(l, 12, 30) {
       const int e = l - 12, m = e >= 9, j = e - 9 * m;
-      double f;
-      if (j < 3) f = m ? fma(B[3], hd->Y[j], hd->Y[40 + j]) : fma(B[0], hd->Y[j], fma(B[1], hd->Y[4 + j], fma(B[2], hd->Y[8 + j], hd->Y[36 + j])));
-      else f = Yb[j * 2 + m] + Pf[81 + e];
-      hd->Fc[e] = f;
-      c.F[18 * k + e] = f;
+      const int j3 = j < 3 ? j : 0;
+      // j < 3: (B'Y)[m][j] + Y[9 + m][j];  else Yb[j][m] + Pvx[m][j]
+      const double fl = m ? fma(B3, hd->Y[j3], hd->Y[40 + j3]) : fma(B0, hd->Y[j3], fma(B1, hd->Y[4 + j3], fma(B2, hd->Y[8 + j3], hd->Y[36 + j3])));
+      const double fh = Yb[j * 2 + m] + Pf[81 + e];
+      const double f = j < 3 ? fl : fh;
+      if (l_ok) { hd->Fc[e] = f; c.F[18 * k + e] = f; }
     }
-    Q3_ITEMS(l, 30, 31) { c.Wi[4 * k] = W00; c.Wi[4 * k + 1] = W01; c.Wi[4 * k + 2] = W11; }
-    Q3_ITEMS(l, 31, 32) { c.zk[2 * k] = z0; c.zk[2 * k + 1] = z1; }
+    Q3_PREDS(l, 30, 31) { if (l_ok) { c.Wi[4 * k] = W00; c.Wi[4 * k + 1] = W01; c.Wi[4 * k + 2] = W11; } }
+    Q3_PREDS(l, 31, 32) { if (l_ok) { c.zk[2 * k] = z0; c.zk[2 * k + 1] = z1; } }
     Q3_SYNC();
     // ---- phase 3
     if (k > 0) {
       const double* Fc = hd->Fc;
-      Q3_ITEM(e, 45) {
-        const int ij = hd->tri[e], i = ij >> 4, j = ij & 15;
+      const double* wk = c.Weff + 10 * (k - 1);
+      Q3_PRED2(e, 45) {
+        const int i = Q3_LOCAL_AT(t_i, e), j = Q3_LOCAL_AT(t_j, e), w = Q3_LOCAL_AT(t_w, e);
         const double f0i = Fc[i], f1i = Fc[9 + i], f0j = Fc[j], f1j = Fc[9 + j];
         const double T = j < 3 ? hd->TA[i * 3 + j] : (i < 3 ? hd->Y[j * 4 + i] : Pf[i * 9 + j]);
-        const double v = T - (W00 * (f0i * f0j) + W01 * (f0i * f1j + f1i * f0j) + W11 * (f1i * f1j)) + qt3(c, k - 1, e);
-        Pf[i * 9 + j] = v; Pf[j * 9 + i] = v;
+        const double qt = Q3_LOCAL_AT(t_q, e) + (w >= 0 ? wk[w >= 0 ? w : 0] : 0.0);
+        const double v = T - (W00 * (f0i * f0j) + W01 * (f0i * f1j + f1i * f0j) + W11 * (f1i * f1j)) + qt;
+        if (e_ok) { Pf[i * 9 + j] = v; Pf[j * 9 + i] = v; }
       }
-      Q3_ITEM(e, 18) {
+      Q3_PRED(e, 18) {
         const int m = e >= 9, j = e - 9 * m;
         const double fw0 = W00 * Fc[j] + W01 * Fc[9 + j], fw1 = W01 * Fc[j] + W11 * Fc[9 + j];
-        Pf[81 + e] = dR2[m * 2] * fw0 + dR2[m * 2 + 1] * fw1;
+        if (e_ok) Pf[81 + e] = dR2[m * 2] * fw0 + dR2[m * 2 + 1] * fw1;
       }
-      Q3_ITEM(j, 9) px[j] = (j < 3 ? hd->Apx[j] : hd->pe[j]) - Fc[j] * z0 - Fc[9 + j] * z1 + c.gx[9 * (k - 1) + j];
-      Q3_ITEMS(l, 9, 11) { const int m = l - 9; pv[m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1; }
-      Q3_ITEMS(l, 11, 14) {
+      Q3_PRED(j, 9) {
+        const double v = (j < 3 ? hd->Apx[j < 3 ? j : 0] : hd->pe[j]) - Fc[j] * z0 - Fc[9 + j] * z1 + c.gx[9 * (k - 1) + j];
+        if (j_ok) px[j] = v;
+      }
+      Q3_PREDS(l, 9, 11) { const int m = l - 9; if (l_ok) pv[m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1; }
+      Q3_PREDS(l, 11, 14) {
         const int q = l - 11, m = q == 2, n = q != 0;  // (0,0) (0,1) (1,1)
         const double a0 = dR2[m * 2] * W00 + dR2[m * 2 + 1] * W01, a1 = dR2[m * 2] * W01 + dR2[m * 2 + 1] * W11;
         const double v = dR2[m * 2 + n] - (a0 * dR2[n] + a1 * dR2[2 + n]);
-        hd->Pvv[m * 2 + n] = v; hd->Pvv[n * 2 + m] = v;
+        if (l_ok) { hd->Pvv[m * 2 + n] = v; hd->Pvv[n * 2 + m] = v; }
       }
-      if (defects) Q3_ITEMS(l, 14, 23) hd->dbuf[(k - 1) & 1][l - 14] = defect3(c, k - 1, l - 14);
+      Q3_PREDS(l, 14, 23) { const double v = defects ? c.dlam[9 * (k - 1) + (l - 14)] : 0.0; if (l_ok) hd->dbuf[(k - 1) & 1][l - 14] = v; }
     }
     Q3_SYNC();
   }
@@ -629,26 +692,31 @@ Q3D void ric_affine_backward3(const Ctx3& c, double* ye, const int fb = 1) {
   int cur = 0;
 #pragma unroll 1
   for (int k = N - 1; k >= 0; --k) {
-    const double* A = c.Acol + 27 * k;
+    const double* A = c.Acol + Q3_AS * k;
     const double* B = c.Bcol + 4 * k;
     const double* pin = hd->px[cur];
     const double* pvin = hd->pv[cur];
     const double* Fk = c.F + 18 * k;
-    const double hu0 = c.gu[2 * k] + pvin[0] + fma(B[0], pin[0], fma(B[1], pin[1], B[2] * pin[2]));
-    const double hu1 = c.gu[2 * k + 1] + pvin[1] + B[3] * pin[0];
+    // what does not depend on the recursion first (the loads overlap the previous stage's barrier)
+    const double B0 = B[0], B1 = B[1], B2 = B[2], B3 = B[3];
+    const double gu0 = c.gu[2 * k], gu1 = c.gu[2 * k + 1];
     const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
+    const double hu0 = gu0 + pvin[0] + fma(B0, pin[0], fma(B1, pin[1], B2 * pin[2]));
+    const double hu1 = gu1 + pvin[1] + B3 * pin[0];
     const double z0 = fb ? W00 * hu0 + W01 * hu1 : 0.0, z1 = fb ? W01 * hu0 + W11 * hu1 : 0.0;
-    Q3_ITEM(j, 9) {
-      double v = pin[j];
-      if (j < 3) {
-        double a0 = 0.0, a1 = 0.0;
+    Q3_PRED(j, 9) {
+      const int j3 = j < 3 ? j : 0;
+      const double f0 = Fk[j], f1 = Fk[9 + j];
+      const double gxm = c.gx[9 * (k > 0 ? k - 1 : 0) + j];
+      double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-        for (int q = 0; q < 8; q += 2) { a0 = fma(A[3 * q + j], pin[q], a0); a1 = fma(A[3 * q + 3 + j], pin[q + 1], a1); }
-        v = fma(A[24 + j], pin[8], a0) + a1;
-      }
-      if (ye) ye[12 * (k + 1) + j] = -pin[j];
-      if (k > 0) hd->px[cur ^ 1][j] = v - Fk[j] * z0 - Fk[9 + j] * z1 + c.gx[9 * (k - 1) + j];
-      else if (ye) {
+      for (int q = 0; q < 8; q += 2) { a0 = fma(A[3 * q + j3], pin[q], a0); a1 = fma(A[3 * q + 3 + j3], pin[q + 1], a1); }
+      a0 = fma(A[24 + j3], pin[8], a0) + a1;
+      const double pj = pin[j];
+      const double v = j < 3 ? a0 : pj;
+      if (ye && j_ok) ye[12 * (k + 1) + j] = -pj;
+      if (k > 0) { if (j_ok) hd->px[cur ^ 1][j] = v - f0 * z0 - f1 * z1 + gxm; }
+      else if (ye && j_ok) {
         double gq = j == 0 ? hd->q0 : 0.0;
         for (int q = 0; q < hd->nq; ++q) {
           const int e = hd->nzl[q], qi = hd->tri[e] >> 4, qj = hd->tri[e] & 15;
@@ -658,8 +726,8 @@ Q3D void ric_affine_backward3(const Ctx3& c, double* ye, const int fb = 1) {
         ye[j] = -(v + gq);
       }
     }
-    Q3_ITEMS(l, 9, 11) { const int m = l - 9; hd->pv[cur ^ 1][m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1; }
-    Q3_ITEMS(l, 11, 12) { c.zk[2 * k] = z0; c.zk[2 * k + 1] = z1; }
+    Q3_PREDS(l, 9, 11) { const int m = l - 9; if (l_ok) hd->pv[cur ^ 1][m] = dR2[m * 2] * z0 + dR2[m * 2 + 1] * z1; }
+    Q3_PREDS(l, 11, 12) { if (l_ok) { c.zk[2 * k] = z0; c.zk[2 * k + 1] = z1; } }
     Q3_SYNC();
     cur ^= 1;
   }
@@ -673,38 +741,46 @@ Q3D void ric_forward3(const Ctx3& c, const int defects) {
   const double* dR2 = hd->dR2;
   double* fx = hd->Y;        // the running stage's step (ping-pong 2 x 9, 2 x 2): over the backward sweeps' scratch
   double* fu = hd->Y + 18;
+  Q3_ITEM(e, 9) fx[e] = 0.0;   // dx_0 = 0, dv_0 = 0: stage 0 runs the same code as the others
+  Q3_ITEM(e, 2) fu[e] = 0.0;
+  Q3_SYNC();
   int cur = 0;
 #pragma unroll 1
   for (int k = 0; k < c.N; ++k) {
-    const double* A = c.Acol + 27 * k;
+    const double* A = c.Acol + Q3_AS * k;
     const double* B = c.Bcol + 4 * k;
     const double* Fk = c.F + 18 * k;
     const double* xin = fx + 9 * cur;
     const double* vin = fu + 2 * cur;
-    double du0 = -c.zk[2 * k], du1 = -c.zk[2 * k + 1];
-    if (k > 0) {
-      double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+    // what does not depend on the recursion first (the loads overlap the previous stage's barrier)
+    double f[18];
 #pragma unroll
-      for (int l = 0; l < 8; l += 2) {
-        t0 = fma(Fk[l], xin[l], t0); t1 = fma(Fk[l + 1], xin[l + 1], t1);
-        t2 = fma(Fk[9 + l], xin[l], t2); t3 = fma(Fk[9 + l + 1], xin[l + 1], t3);
-      }
-      const double r0 = fma(Fk[8], xin[8], t0) + t1 - (dR2[0] * vin[0] + dR2[1] * vin[1]);
-      const double r1 = fma(Fk[17], xin[8], t2) + t3 - (dR2[2] * vin[0] + dR2[3] * vin[1]);
-      const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
-      du0 -= W00 * r0 + W01 * r1;
-      du1 -= W01 * r0 + W11 * r1;
+    for (int l = 0; l < 18; ++l) f[l] = Fk[l];
+    const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
+    const double zk0 = c.zk[2 * k], zk1 = c.zk[2 * k + 1];
+    const double B0 = B[0], B1 = B[1], B2 = B[2], B3 = B[3];
+    double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+#pragma unroll
+    for (int l = 0; l < 8; l += 2) {
+      t0 = fma(f[l], xin[l], t0); t1 = fma(f[l + 1], xin[l + 1], t1);
+      t2 = fma(f[9 + l], xin[l], t2); t3 = fma(f[9 + l + 1], xin[l + 1], t3);
     }
-    Q3_ITEM(j, 9) {
-      double v = (k > 0 ? arow3(A, xin, j) : 0.0) + brow3(B, du0, du1, j);
-      if (defects) v += defect3(c, k, j);
-      fx[9 * (cur ^ 1) + j] = v;
-      c.dx[9 * k + j] = v;
+    const double r0 = fma(f[8], xin[8], t0) + t1 - (dR2[0] * vin[0] + dR2[1] * vin[1]);
+    const double r1 = fma(f[17], xin[8], t2) + t3 - (dR2[2] * vin[0] + dR2[3] * vin[1]);
+    const double du0 = -zk0 - (W00 * r0 + W01 * r1);
+    const double du1 = -zk1 - (W01 * r0 + W11 * r1);
+    Q3_PRED(j, 9) {
+      const double a0 = A[j * 3], a1 = A[j * 3 + 1], a2 = A[j * 3 + 2];
+      const double dj = defects ? c.dlam[9 * k + j] : 0.0;
+      const double bj0 = j == 0 ? B0 : (j == 1 ? B1 : (j == 2 ? B2 : 0.0)), bj1 = j == 0 ? B3 : 0.0;
+      double v = j >= 3 ? xin[j] : 0.0;
+      v = fma(a0, xin[0], v); v = fma(a1, xin[1], v); v = fma(a2, xin[2], v);
+      v += fma(bj0, du0, bj1 * du1) + dj;
+      if (j_ok) { fx[9 * (cur ^ 1) + j] = v; c.dx[9 * k + j] = v; }
     }
-    Q3_ITEMS(l, 9, 11) {
+    Q3_PREDS(l, 9, 11) {
       const double v = l == 9 ? du0 : du1;
-      fu[2 * (cur ^ 1) + (l - 9)] = v;
-      c.du[2 * k + (l - 9)] = v;
+      if (l_ok) { fu[2 * (cur ^ 1) + (l - 9)] = v; c.du[2 * k + (l - 9)] = v; }
     }
     Q3_SYNC();
     cur ^= 1;
@@ -732,6 +808,7 @@ Q3N void factor_solve3(int mode, int defects) {
   Q3_CTX(c);
   stage_weights3(c);
   assemble_gradient3(c, mode, 0.0);
+  if (defects) stage_defects3(c);
   ric_factor_backward3(c, defects);
   ric_forward3(c, defects);
   if (Q3_LANE == 0) { ++c.hd->n_fact; ++c.hd->n_solve; }
