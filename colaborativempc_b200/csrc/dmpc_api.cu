@@ -197,6 +197,14 @@ static int launch_shift_pack(dmpc_handle* h, int32_t B, const double* d_z, const
 // One batch: the solve and, with `next`, the caller's bookkeeping.  Stage-wise engine: one launch does both.
 // Condensed engine: its (split) launch, then the stage-wise kernel over the QPs it reported DMPC_UNSOLVED (numerical
 // breakdown of the condensed factorisation - crawling vehicles), then the shift kernel.
+// Input staging of the stage-wise kernel: bulk async copies (TMA) into shared memory unless DMPC_B200_BULK_IN=0
+// (development switch for A/B measurements; results are identical either way).
+static int bulk_in_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DMPC_B200_BULK_IN"); v = !(e && e[0] == '0'); }
+  return v;
+}
+
 static int solve_impl(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_io* next, void* stream) {
   if (!h || !io) return DMPC_ERR_ARG;
   if (io->B == 0) return DMPC_OK;
@@ -237,6 +245,7 @@ static int solve_impl(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_
       }
       bp.warm = h->d_warm; bp.warm_shift = h->opt.warm_start == 2;
     }
+    bp.bulk_in = bulk_in_enabled();
     lpv_qp_stage_kernel<<<io->B, QP3_THREADS, h->stage_smem, st>>>(h->P, bp);
     h->launches++;
     if (hint) {
@@ -283,6 +292,7 @@ static int solve_impl(dmpc_handle* h, const dmpc_batch_io* io, const dmpc_shift_
     if (h->stage_ok && io->status) {  // what the condensed factorisation could not handle is solved stage-wise
       bp.order = nullptr; bp.cost = nullptr; bp.nhard = nullptr; bp.part = 0;
       bp.only_status = DMPC_UNSOLVED;
+      bp.bulk_in = bulk_in_enabled();
       lpv_qp_stage_kernel<<<io->B, QP3_THREADS, h->stage_smem, st>>>(h->P, bp);
       h->launches++;
     }
@@ -513,13 +523,12 @@ extern "C" int dmpc_sim_batch(dmpc_handle* h, int32_t B, const double* d_xpred, 
                               int32_t* d_status, void* stream) {
   if (!h || B < 0 || (B > 0 && (!d_xpred || !d_u || !d_out))) return DMPC_ERR_ARG;
   if (B == 0) return DMPC_OK;
-  const size_t smem = (size_t)SIM_WARPS * SIM_GROUP * h->P.N * 30 * sizeof(double);
+  const size_t smem = sim_smem_bytes(h->P.N);
   if (smem > 48 * 1024 && !h->sim_attr) {
     CUDA_TRY(h, cudaFuncSetAttribute(lpv_sim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     h->sim_attr = 1;
   }
-  const int per_cta = SIM_WARPS * SIM_GROUP;
-  lpv_sim_kernel<<<(B + per_cta - 1) / per_cta, 32 * SIM_WARPS, smem, (cudaStream_t)stream>>>(h->P, B, d_xpred, d_u, d_out, d_status);
+  lpv_sim_kernel<<<(B + SIM_TILE - 1) / SIM_TILE, SIM_THREADS, smem, (cudaStream_t)stream>>>(h->P, B, d_xpred, d_u, d_out, d_status);
   h->launches++;
   CUDA_TRY(h, cudaGetLastError());
   return DMPC_OK;
@@ -707,6 +716,7 @@ extern "C" int dmpc_solve_batch_static(const dmpc_params* p, const dmpc_options*
   bp.status = io->status; bp.iters = io->iters; bp.pivots = io->pivots;
   bp.gws = g_static_ptr[device]; bp.gws_stride = (long long)stride;
   // nothing is carried between calls here: no launch order, no warm start (those live in handle-owned buffers)
+  bp.bulk_in = bulk_in_enabled();
   lpv_qp_stage_kernel<<<io->B, QP3_THREADS, smem, (cudaStream_t)stream>>>(P, bp);
   if ((e = cudaGetLastError()) != cudaSuccess) return static_fail(err, err_len, DMPC_ERR_CUDA, "CUDA: ", cudaGetErrorString(e));
   return DMPC_OK;

@@ -6,93 +6,164 @@
 //   result = [x_1 .. x_N, ones(9)]  (np.delete(xPred, 0, 0) + a row of ones).
 // get_ey is evaluated on every row of xPred by the reference (its value is unused here, a failed lookup raises).
 //
-// One warp per THREE models: a lane linearises one (model, stage) pair (rows of xPred are contiguous, so a warp reads
-// them coalesced) into shared memory - the 9x3 column block of A_k and the input term B_k u_k, 30 doubles - then lanes
-// 9g..9g+8 carry the nine states of model g through the N sequential steps (the three non-trivial columns of A_k are
-// broadcast by shuffle inside the group) and write each predicted row as one 72-byte segment.  HBM traffic =
-// compulsory: (N+1)*72 + N*16 bytes read, (N+1)*72 + 4 written per model.
+// A pure streaming op: (N+1)*72 + N*16 bytes read, (N+1)*72 + 4 written per model, HBM-bound by construction.  One
+// 64-thread CTA per TILE of SIM_TILE consecutive models, whose inputs and outputs are single contiguous byte ranges:
+//   1  one thread stages the tile's xPred rows and inputs in shared memory with two bulk async copies (TMA,
+//      cp.async.bulk + mbarrier) - full-line reads, no per-lane address arithmetic;
+//   2  one lane per (model, stage) pair linearises it into 17 doubles (the 3 x 3 block of A_k that feeds back, the input
+//      term B_k u_k, the ten non-trivial coefficients of the six integrator rows) - all 64 lanes busy on the sincos /
+//      division work, conflict-free strides (9, 17);
+//   3  one lane per MODEL carries its nine states through the N sequential steps in registers (30 FMAs a step, no
+//      shuffles, no barriers) and overwrites the tile in place with the predicted rows;
+//   4  one thread writes the tile back with one bulk async store - full-line writes instead of 72-byte row fragments.
+// Several CTAs per SM are in different phases at any time, which is what overlaps the copies with the arithmetic.
+// A tile whose byte ranges are not 16-byte multiples (odd tail tile, unaligned caller pointers) takes plain loads / stores.
 #pragma once
 #include "qp_common.cuh"
 
-#define SIM_WARPS 2
-#define SIM_GROUP 3  // models per warp
+#define SIM_TILE 8
+#define SIM_THREADS 64
+#define SIM_ABS 17  // doubles per (model, stage)
 
-__global__ void __launch_bounds__(32 * SIM_WARPS) lpv_sim_kernel(const __grid_constant__ DevParams P, int B,
-                                                                   const double* __restrict__ xpred, const double* __restrict__ u,
-                                                                   double* __restrict__ out, int* __restrict__ status) {
-  extern __shared__ __align__(16) double sim_sm[];  // per warp: SIM_GROUP x N x 30
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b0 = (blockIdx.x * SIM_WARPS + warp) * SIM_GROUP;
+// shared-memory layout (doubles after the 16-byte barrier slot): tile [T][N+1][9] | u [T][N][2] | AB [T][17 N + 1] | bad [T] ints
+__host__ __device__ inline size_t sim_smem_bytes(int N) {
+  size_t d = (size_t)SIM_TILE * (N + 1) * 9;
+  d = (d + 1) & ~(size_t)1;
+  d += (size_t)SIM_TILE * N * 2;
+  d += (size_t)SIM_TILE * (SIM_ABS * N + 1);
+  return 16 + d * sizeof(double) + SIM_TILE * sizeof(int);
+}
+
+__device__ __forceinline__ void sim_linearise(const DevParams& P, const double* x, double delta, double acc, double cur, double* A) {
+  const double vx = x[0], vy = x[1], ey = x[3], epsi = x[4], theta = x[5];
+  double sd, cd, se, ce, st, ct;
+  sincos(delta, &sd, &cd); sincos(epsi, &se, &ce); sincos(theta, &st, &ct);
+  const double imvx = 1.0 / (P.m * vx), iIvx = 1.0 / (P.I * vx);
+  const double A12 = (sd * P.Cf) * imvx;
+  const double A13 = (sd * P.Cf * P.lf) * imvx + vy;
+  const double A22 = -(P.Cr + P.Cf * cd) * imvx;
+  const double A23 = -(P.lf * P.Cf * cd - P.lr * P.Cr) * imvx - vx;
+  const double A32 = -(P.lf * P.Cf * cd - P.lr * P.Cr) * iIvx;
+  const double A33 = -(P.lf * P.lf * P.Cf * cd + P.lr * P.lr * P.Cr) * iIvx;
+  const double B11 = -(sd * P.Cf) / P.m;
+  const double iden = 1.0 / (1.0 - ey * cur);
+  const double dt = P.dt;
+  // rows 0-2 of A_k = I + dt Ac, columns 1-2 (column 0 is (1 - dt mu, 0, 0))
+  A[0] = dt * A12; A[1] = dt * A13;
+  A[2] = 1.0 + dt * A22; A[3] = dt * A23;
+  A[4] = dt * A32; A[5] = 1.0 + dt * A33;
+  // B_k u_k: only the first three states have an input term
+  A[6] = fma(dt * B11, delta, dt * acc);
+  A[7] = dt * ((cd * P.Cf) / P.m) * delta;
+  A[8] = dt * ((P.lf * P.Cf * cd) / P.I) * delta;
+  // integrator rows: e_y (vx, vy), e_psi (vx, vy; w has dt), s (vx, vy), x and y (vx, vy)
+  A[9] = dt * se; A[10] = dt * ce;
+  A[11] = dt * (iden * (-ce * cur)); A[12] = dt * (iden * (se * cur));
+  A[13] = dt * (ce * iden); A[14] = dt * (-se * iden);
+  A[15] = dt * ct; A[16] = dt * st;
+}
+
+__global__ void __launch_bounds__(SIM_THREADS) lpv_sim_kernel(const __grid_constant__ DevParams P, int B,
+                                                                const double* __restrict__ xpred, const double* __restrict__ u,
+                                                                double* __restrict__ out, int* __restrict__ status) {
+  extern __shared__ __align__(16) char sim_raw[];
+  const int N = P.N, tid = threadIdx.x;
+  const int b0 = blockIdx.x * SIM_TILE;
   if (b0 >= B) return;
-  const int N = P.N;
-  const int nm = min(SIM_GROUP, B - b0);  // models of this warp
-  double* AB = sim_sm + (size_t)warp * SIM_GROUP * N * 30;
-  unsigned badmask = 0;  // bit g: a map lookup of model g failed
-  for (int t = lane; t < nm * (N + 1); t += 32) {
-    const int g = t / (N + 1), k = t - g * (N + 1);
-    const double* x = xpred + ((size_t)(b0 + g) * (N + 1) + k) * NSTATE;
+  const int nm = min(SIM_TILE, B - b0);  // models of this tile
+  const int rowd = (N + 1) * NSTATE;     // doubles of one model's rows
+  unsigned long long* mbar = (unsigned long long*)sim_raw;
+  double* tile = (double*)(sim_raw + 16);
+  double* ut = tile + (((size_t)SIM_TILE * rowd + 1) & ~(size_t)1);
+  double* AB = ut + (size_t)SIM_TILE * N * 2;
+  int* bad = (int*)(AB + (size_t)SIM_TILE * (SIM_ABS * N + 1));
+  const int abm = SIM_ABS * N + 1;       // odd stride between the models' blocks
+  const double* gx = xpred + (size_t)b0 * rowd;
+  const double* gu = u + (size_t)b0 * N * 2;
+  double* go = out + (size_t)b0 * rowd;
+  const unsigned xbytes = (unsigned)nm * rowd * 8u, ubytes = (unsigned)nm * N * 16u;
+  // bulk copies need 16-byte aligned addresses and sizes (a full tile of 8 models always has them for aligned arrays)
+  const bool bulk = ((((size_t)gx | (size_t)gu | (size_t)go) & 15) == 0) && (xbytes & 15) == 0;
+  if (tid < SIM_TILE) bad[tid] = 0;
+
+  // ---- 1: stage the tile
+  if (bulk) {
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(mbar);
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(xbytes + ubytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                       (unsigned)__cvta_generic_to_shared(tile)), "l"(gx), "r"(xbytes), "r"(bar) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                       (unsigned)__cvta_generic_to_shared(ut)), "l"(gu), "r"(ubytes), "r"(bar) : "memory");
+    }
+    __syncthreads();  // the barrier is initialised before anyone polls it
+    unsigned done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
+  } else {
+    for (int i = tid; i < nm * rowd; i += SIM_THREADS) tile[i] = gx[i];
+    for (int i = tid; i < nm * N * 2; i += SIM_THREADS) ut[i] = gu[i];
+    __syncthreads();
+  }
+
+  // ---- 2: one lane per (model, row): map lookup on every row, linearisation on rows 0 .. N-1
+  for (int t = tid; t < nm * (N + 1); t += SIM_THREADS) {
+    const int m = t / (N + 1), k = t - m * (N + 1);
+    const double* x = tile + (size_t)t * NSTATE;
     const int seg = map_segment(P, x[6]);
-    if (seg < 0) { badmask |= 1u << g; continue; }
-    if (k == N) continue;  // row N: only the get_ey lookup
-    const double* uk = u + ((size_t)(b0 + g) * N + k) * 2;
-    const double vx = x[0], vy = x[1], ey = x[3], epsi = x[4], theta = x[5];
-    const double cur = P.seg_curv[seg];
-    const double delta = uk[0], acc = uk[1];
-    double sd, cd, se, ce, st, ct;
-    sincos(delta, &sd, &cd); sincos(epsi, &se, &ce); sincos(theta, &st, &ct);
-    const double imvx = 1.0 / (P.m * vx), iIvx = 1.0 / (P.I * vx);
-    const double A12 = (sd * P.Cf) * imvx;
-    const double A13 = (sd * P.Cf * P.lf) * imvx + vy;
-    const double A22 = -(P.Cr + P.Cf * cd) * imvx;
-    const double A23 = -(P.lf * P.Cf * cd - P.lr * P.Cr) * imvx - vx;
-    const double A32 = -(P.lf * P.Cf * cd - P.lr * P.Cr) * iIvx;
-    const double A33 = -(P.lf * P.lf * P.Cf * cd + P.lr * P.lr * P.Cr) * iIvx;
-    const double B11 = -(sd * P.Cf) / P.m;
-    const double iden = 1.0 / (1.0 - ey * cur);
-    const double Ac[27] = {-P.mu, A12, A13,
-                           0.0, A22, A23,
-                           0.0, A32, A33,
-                           se, ce, 0.0,
-                           iden * (-ce * cur), iden * (se * cur), 1.0,
-                           0.0, 0.0, 1.0,
-                           ce * iden, -se * iden, 0.0,
-                           ct, -st, 0.0,
-                           st, ct, 0.0};
-    double* A = AB + ((size_t)g * N + k) * 30;
-#pragma unroll
-    for (int r = 0; r < 9; ++r)
-#pragma unroll
-      for (int j = 0; j < 3; ++j) A[r * 3 + j] = (r == j ? 1.0 : 0.0) + P.dt * Ac[r * 3 + j];
-    // B_k u_k: only the first three states have an input term
-    A[27] = fma(P.dt * B11, delta, P.dt * acc);
-    A[28] = P.dt * ((cd * P.Cf) / P.m) * delta;
-    A[29] = P.dt * ((P.lf * P.Cf * cd) / P.I) * delta;
+    if (seg < 0) { bad[m] = 1; continue; }  // benign race: every writer stores 1
+    if (k == N) continue;                   // row N: only the get_ey lookup
+    const double2 uk = *(const double2*)(ut + ((size_t)m * N + k) * 2);
+    sim_linearise(P, x, uk.x, uk.y, P.seg_curv[seg], AB + (size_t)m * abm + (size_t)k * SIM_ABS);
   }
+  __syncthreads();
+
+  // ---- 3: one lane per model: the N sequential steps in registers, rows written over the tile in place
+  if (tid < nm) {
+    const int m = tid;
+    double* rows = tile + (size_t)m * rowd;
+    const double* Am = AB + (size_t)m * abm;
+    const double a00 = 1.0 + P.dt * (-P.mu), dt = P.dt;
+    const bool isbad = bad[m] != 0;
+    const double qnan = __longlong_as_double(0x7ff8000000000000ULL);
+    double v[NSTATE];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) badmask |= __shfl_xor_sync(0xffffffffu, badmask, o);
-  __syncwarp();
-  // lanes 9g .. 9g+8: state r of model g
-  const int g = lane / NSTATE, r = lane - g * NSTATE;
-  const bool live = g < nm;
-  const bool bad = live && ((badmask >> g) & 1u);
-  const int gb = live ? g : 0;
-  const double* xp = xpred + (size_t)(b0 + gb) * (N + 1) * NSTATE;
-  double* o = out + (size_t)(b0 + gb) * (N + 1) * NSTATE;
-  const double qnan = __longlong_as_double(0x7ff8000000000000ULL);
-  double v = xp[r];
-  const int base = g * NSTATE;  // first lane of the group (lanes 27..31 shuffle among themselves, unused)
+    for (int j = 0; j < NSTATE; ++j) v[j] = rows[j];
 #pragma unroll 2
-  for (int k = 0; k < N; ++k) {
-    const double* A = AB + ((size_t)gb * N + k) * 30;
-    const double v0 = __shfl_sync(0xffffffffu, v, base), v1 = __shfl_sync(0xffffffffu, v, base + 1),
-                 v2 = __shfl_sync(0xffffffffu, v, base + 2);
-    double s = (r >= 3) ? v : A[27 + r];
-    s = fma(A[r * 3 + 0], v0, s); s = fma(A[r * 3 + 1], v1, s); s = fma(A[r * 3 + 2], v2, s);
-    v = s;
-    if (live) o[k * NSTATE + r] = bad ? qnan : v;  // row k of the result = x_{k+1}; the reference raises on a failed lookup
+    for (int k = 0; k < N; ++k) {
+      const double* A = Am + (size_t)k * SIM_ABS;
+      const double v0 = v[0], v1 = v[1], v2 = v[2];
+      // same evaluation order per row as A_k x_k + B_k u_k with the zero entries left out
+      v[0] = fma(A[1], v2, fma(A[0], v1, fma(a00, v0, A[6])));
+      v[1] = fma(A[3], v2, fma(A[2], v1, A[7]));
+      v[2] = fma(A[5], v2, fma(A[4], v1, A[8]));
+      v[3] = fma(A[10], v1, fma(A[9], v0, v[3]));
+      v[4] = fma(dt, v2, fma(A[12], v1, fma(A[11], v0, v[4])));
+      v[5] = fma(dt, v2, v[5]);
+      v[6] = fma(A[14], v1, fma(A[13], v0, v[6]));
+      v[7] = fma(-A[16], v1, fma(A[15], v0, v[7]));
+      v[8] = fma(A[15], v1, fma(A[16], v0, v[8]));
+#pragma unroll
+      for (int j = 0; j < NSTATE; ++j) rows[k * NSTATE + j] = isbad ? qnan : v[j];  // row k of the result = x_{k+1}
+    }
+#pragma unroll
+    for (int j = 0; j < NSTATE; ++j) rows[N * NSTATE + j] = isbad ? qnan : 1.0;  // the reference raises on a failed lookup
+    if (status) status[b0 + m] = isbad ? DMPC_MAP_LOOKUP_FAILED : 0;
   }
-  if (live) {
-    o[N * NSTATE + r] = bad ? qnan : 1.0;
-    if (r == 0 && status) status[b0 + g] = bad ? DMPC_MAP_LOOKUP_FAILED : 0;
+
+  // ---- 4: write the tile back
+  if (bulk) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the generic-proxy writes above, before the async copy reads them
+    __syncthreads();
+    if (tid == 0) {
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(go), "r"((unsigned)__cvta_generic_to_shared(tile)), "r"(xbytes) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // shared memory stays valid until the copy has read it
+    }
+  } else {
+    __syncthreads();
+    for (int i = tid; i < nm * rowd; i += SIM_THREADS) go[i] = tile[i];
   }
 }

@@ -90,7 +90,9 @@ extern __shared__ __align__(16) char smem_stage[];
 #endif
 
 // lane-strided item loop: on the device the 32 lanes share the items, on the host one "lane" walks them all
-#define Q3_FOR(i, n) for (int i = Q3_LANE; i < (n); i += Q3_NL)
+// (not unrolled: the kernel is 20 k instructions, its warps sit in different loops, and instruction fetch - 12 % of the
+// stall samples with these loops unrolled four times - costs more than the unrolling gains)
+#define Q3_FOR(i, n) _Pragma("unroll 1") for (int i = Q3_LANE; i < (n); i += Q3_NL)
 
 // Header at the start of the workspace: sizes, options, the cost / limit constants and the small Riccati scratch.
 struct Hdr3 {
@@ -115,6 +117,7 @@ struct Hdr3 {
   double TA[9], Apx[3], Fc[18];
   double dbuf[2][9];        // dynamics defect of the stage being processed / the next one
   unsigned long long hist[8];
+  unsigned long long mbar;  // mbarrier of the bulk input copies (device)
   unsigned char tri[48];  // (i << 4) | j of the 45 upper-triangle pairs of a 9 x 9 matrix
   unsigned char wix[48];  // index into the stage's Weff of pair e (outputs 0, 3, 7, 8), 255 = none
   unsigned char nzl[48];  // the nq pairs e with 2 Q != 0
@@ -251,6 +254,7 @@ Q3D void eval_residuals3(const Ctx3& c) {
     r[1] = (xk[0] - lim[1]) + sk[0];
     r[2] = (xk[3] - c.eyb[k]) + sk[1];
     r[3] = (-xk[3] - c.eyb[k]) + sk[1];
+#pragma unroll 1
     for (int i = 0; i < c.nn; ++i) {
       const int q = k * c.nn + i;
       r[4 + i] = i < c.cnt ? fma(c.ax[q], xk[7] - c.mx[q], c.ay[q] * (xk[8] - c.my[q])) + (hm - sk[2]) : -1.0;
@@ -289,6 +293,7 @@ Q3D int setup_planes3(const Ctx3& c, const DevParams& P, const double* nbr, cons
     const double ex = pose[2 * h], ey = pose[2 * h + 1];
     const double fx = pose[2 * (h + 1)], fy = pose[2 * (h + 1) + 1];
     double sx = 0.0, sy = 0.0;
+#pragma unroll 1
     for (int n = 0; n < c.nn; ++n) {
       double ax = 0.0, ay = 0.0, bb = 0.0;
       if (n < c.cnt) {
@@ -391,6 +396,7 @@ Q3D void stage_weights3(const Ctx3& c) {
   Q3_FOR(t, c.N) {
     const double* d = c.D + t * c.rst;
     double sxx = 0, sxy = 0, syy = 0, sx = 0, sy = 0, sd = 0;
+#pragma unroll 1
     for (int i = 0; i < c.cnt; ++i) {
       const double di = d[4 + i], x = c.ax[t * c.nn + i], y = c.ay[t * c.nn + i];
       sxx = fma(di * x, x, sxx); sxy = fma(di * x, y, sxy); syy = fma(di * y, y, syy);
@@ -452,12 +458,14 @@ Q3D void assemble_gradient3(const Ctx3& c, int mode, double smu) {
     const double w0 = row_w3(c, j0, mode, smu), w1 = row_w3(c, j0 + 1, mode, smu);
     const double w2 = row_w3(c, j0 + 2, mode, smu), w3 = row_w3(c, j0 + 3, mode, smu);
     double wx = 0.0, wy = 0.0, ws = 0.0;
+#pragma unroll 1
     for (int i = 0; i < c.cnt; ++i) {
       const double wi = row_w3(c, j0 + 4 + i, mode, smu);
       wx = fma(c.ax[k * c.nn + i], wi, wx); wy = fma(c.ay[k * c.nn + i], wi, wy); ws += wi;
     }
     double* g = c.gx + 9 * k;
     for (int i = 0; i < 9; ++i) g[i] = 0.0;
+#pragma unroll 1
     for (int q = 0; q < hd->nq; ++q) {
       const int e = hd->nzl[q], i = hd->tri[e] >> 4, j = hd->tri[e] & 15;
       g[i] = fma(hd->Q2u[e], xk1[j], g[i]);
@@ -718,7 +726,8 @@ Q3D void ric_affine_backward3(const Ctx3& c, double* ye, const int fb = 1) {
       if (k > 0) { if (j_ok) hd->px[cur ^ 1][j] = v - f0 * z0 - f1 * z1 + gxm; }
       else if (ye && j_ok) {
         double gq = j == 0 ? hd->q0 : 0.0;
-        for (int q = 0; q < hd->nq; ++q) {
+    #pragma unroll 1
+    for (int q = 0; q < hd->nq; ++q) {
           const int e = hd->nzl[q], qi = hd->tri[e] >> 4, qj = hd->tri[e] & 15;
           if (qi == j) gq = fma(hd->Q2u[e], hd->x0[qj], gq);
           else if (qj == j) gq = fma(hd->Q2u[e], hd->x0[qi], gq);

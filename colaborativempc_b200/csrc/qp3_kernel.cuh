@@ -41,9 +41,67 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
   const double* uprev = io.uprev + (size_t)b * N * 2;
   const double* nbr = io.nbr_xy + (size_t)b * (N + 1) * nn * 2;
   const double* pose = io.pose + (size_t)b * (N + 1) * 2;
+#ifndef QP3_HOST
+  // The QP's ~2.9 KB of stacked problem data staged in shared memory by bulk async copies (TMA, cp.async.bulk +
+  // mbarrier): four copies issued by one lane land while the tables are built, instead of ~90 dependent per-lane
+  // loads from HBM (or, with page-locked host buffers, over PCIe).  The staging area is workspace that is not live
+  // before the solve (lam .. res).  A copy covers the 16-byte aligned interior of its array; the odd head / tail
+  // double (Last_xPredicted rows are 72 bytes) is loaded plainly, so nothing outside the QP's own slice is read.
+  if (io.bulk_in && io.xprev_rows <= N + 1) {
+    const double* src[4] = {xprev, uprev, nbr, pose};
+    const int len[4] = {io.xprev_rows * NSTATE, 2 * N, 2 * (N + 1) * nn, 2 * (N + 1)};
+    double* dstv[4];
+    double* stg = c.lam + (((size_t)c.lam >> 3) & 1);  // 16-byte aligned
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(&hd->mbar);
+    if (Q3_LANE == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    unsigned total = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int head = (int)(((size_t)src[q] >> 3) & 1);        // doubles before the first 16-byte boundary
+      dstv[q] = stg + head;                                      // same alignment class as the source
+      stg += (len[q] + head + 1) & ~1;
+      const int body = (len[q] - head) & ~1;                    // doubles of the aligned interior
+      if (body > 0) total += (unsigned)body * 8u;
+    }
+    if (Q3_LANE == 0) {
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(total) : "memory");
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int head = (int)(((size_t)src[q] >> 3) & 1);
+        const int body = (len[q] - head) & ~1;
+        if (body > 0)
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                           (unsigned)__cvta_generic_to_shared(dstv[q] + head)),
+                       "l"(src[q] + head), "r"((unsigned)body * 8u), "r"(bar)
+                       : "memory");
+      }
+    }
+    // head / tail doubles: lanes 0-3 one array each
+    if (Q3_LANE < 4) {
+      const int q = Q3_LANE;
+      const double* s_ = q == 0 ? src[0] : (q == 1 ? src[1] : (q == 2 ? src[2] : src[3]));
+      double* d_ = q == 0 ? dstv[0] : (q == 1 ? dstv[1] : (q == 2 ? dstv[2] : dstv[3]));
+      const int n_ = q == 0 ? len[0] : (q == 1 ? len[1] : (q == 2 ? len[2] : len[3]));
+      const int head = (int)(((size_t)s_ >> 3) & 1);
+      const int body = (n_ - head) & ~1;
+      if (head && n_ > 0) d_[0] = s_[0];
+      if (head + body < n_) d_[n_ - 1] = s_[n_ - 1];
+    }
+    build_tables3(c);  // overlaps the copies
+    unsigned done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar) : "memory");
+    __syncwarp();
+    xprev = dstv[0]; uprev = dstv[1]; nbr = dstv[2]; pose = dstv[3];
+  } else
+#endif
+  build_tables3(c);
 
   // ---------------- problem build ----------------
-  build_tables3(c);
   int bad_plane = setup_planes3(c, P, nbr, pose, io.planes ? io.planes + (size_t)b * N * 3 * nn : nullptr);
   int bad_map = setup_linearise3(c, P, xprev, io.xprev_rows, uprev);
   bad_plane = q3_wor(bad_plane);
@@ -107,6 +165,7 @@ Q3D void solve_one_qp3(const DevParams& P, const BatchPtrs& io, const int b) {
       Q3_FOR(t, N + 1) {
         const double* x = t == 0 ? hd->x0 : c.x + 9 * (t - 1);
         double s = 0.0;
+#pragma unroll 1
         for (int q = 0; q < hd->nq; ++q) {
           const int e = hd->nzl[q], i = hd->tri[e] >> 4, j = hd->tri[e] & 15;
           s = fma((i == j ? 0.5 : 1.0) * hd->Q2u[e] * x[i], x[j], s);

@@ -223,6 +223,7 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     double v_obj = 0.0;
     Q3_FOR(k, c.N) {  // scale of the objective (the exact value is computed by the epilogue)
       const double* xk = c.x + 9 * k;
+#pragma unroll 1
       for (int q = 0; q < hd->nq; ++q) { const int e = hd->nzl[q], i = hd->tri[e] >> 4; if (i == (hd->tri[e] & 15)) v_obj += xk[i] * (0.5 * hd->Q2u[e] * xk[i]); }
       v_obj += hd->q0 * xk[0];
     }

@@ -32,6 +32,7 @@ struct DevParams {
 
 struct BatchPtrs {
   int B, xprev_rows;
+  int bulk_in;              // stage-wise engine: 1 = the per-QP inputs are staged in shared memory by bulk async copies (TMA)
   const double *x0, *xprev, *uprev, *uold, *nbr_xy, *pose;
   const int* nbr_count;
   double *z, *planes, *y_ineq, *y_eq, *obj;
