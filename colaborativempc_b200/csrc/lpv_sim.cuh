@@ -7,11 +7,11 @@
 // get_ey is evaluated on every row of xPred by the reference (its value is unused here, a failed lookup raises).
 //
 // A pure streaming op: (N+1)*72 + N*16 bytes read, (N+1)*72 + 4 written per model, HBM-bound by construction.  One
-// 64-thread CTA per TILE of SIM_TILE consecutive models, whose inputs and outputs are single contiguous byte ranges:
+// 128-thread CTA per TILE of SIM_TILE consecutive models, whose inputs and outputs are single contiguous byte ranges:
 //   1  one thread stages the tile's xPred rows and inputs in shared memory with two bulk async copies (TMA,
 //      cp.async.bulk + mbarrier) - full-line reads, no per-lane address arithmetic;
 //   2  one lane per (model, stage) pair linearises it into 17 doubles (the 3 x 3 block of A_k that feeds back, the input
-//      term B_k u_k, the ten non-trivial coefficients of the six integrator rows) - all 64 lanes busy on the sincos /
+//      term B_k u_k, the ten non-trivial coefficients of the six integrator rows) - every lane busy on the sincos /
 //      division work, conflict-free strides (9, 17);
 //   3  one lane per MODEL carries its nine states through the N sequential steps in registers (30 FMAs a step, no
 //      shuffles, no barriers) and overwrites the tile in place with the predicted rows;
@@ -21,8 +21,12 @@
 #pragma once
 #include "qp_common.cuh"
 
-#define SIM_TILE 8
-#define SIM_THREADS 64
+#ifndef SIM_TILE
+#define SIM_TILE 16   // measured on B200 (N = 20): 8 x 64 threads 42 %, 12 x 64 40 %, 16 x 64 33 %, 16 x 128 45 % of the HBM copy peak
+#endif
+#ifndef SIM_THREADS
+#define SIM_THREADS 128
+#endif
 #define SIM_ABS 17  // doubles per (model, stage)
 
 // shared-memory layout (doubles after the 16-byte barrier slot): tile [T][N+1][9] | u [T][N][2] | AB [T][17 N + 1] | bad [T] ints
@@ -34,19 +38,41 @@ __host__ __device__ inline size_t sim_smem_bytes(int N) {
   return 16 + d * sizeof(double) + SIM_TILE * sizeof(int);
 }
 
-__device__ __forceinline__ void sim_linearise(const DevParams& P, const double* x, double delta, double acc, double cur, double* A) {
+// map_segment (qp_common.cuh) for a track whose segments tile [s0[0], end) exactly - checked on the host, DevParams.seg_tiled:
+// "exactly one segment holds s" is then "s lies in the track" and its index is the number of later starts not above s.
+__device__ __forceinline__ int sim_map_segment(const DevParams& P, double s) {
+  if (!P.seg_tiled) return map_segment(P, s);
+  const double L = P.seg_s0[P.nseg - 1] + P.seg_len[P.nseg - 1];
+  if (!(s == s) || !(L > 0.0) || fabs(s) > 1e6 * L) return -1;
+  if (s > L) {
+    s -= L * floor(s / L);
+    if (s <= 0.0) s += L;
+    while (s > L) s -= L;
+  }
+  if (s < 0.0) s = 0.0;
+  if (!(s >= P.seg_s0[0] && s < L)) return -1;
+  int f = 0;
+#pragma unroll 1
+  for (int i = 1; i < P.nseg; ++i) f += (s >= P.seg_s0[i]) ? 1 : 0;
+  return f;
+}
+
+// inv_m = 1 / m, inv_I = 1 / I.  The per-row reciprocals are branch-free Newton reciprocals (q3_rcp, about one ulp):
+// six IEEE divisions per row were 15 % of this kernel's instructions; the roll-out agrees with the reference to 1e-12.
+__device__ __forceinline__ void sim_linearise(const DevParams& P, const double* x, double delta, double acc, double cur, double* A,
+                                              double inv_m, double inv_I) {
   const double vx = x[0], vy = x[1], ey = x[3], epsi = x[4], theta = x[5];
   double sd, cd, se, ce, st, ct;
   sincos(delta, &sd, &cd); sincos(epsi, &se, &ce); sincos(theta, &st, &ct);
-  const double imvx = 1.0 / (P.m * vx), iIvx = 1.0 / (P.I * vx);
+  const double ivx = q3_rcp(vx), imvx = ivx * inv_m, iIvx = ivx * inv_I;
   const double A12 = (sd * P.Cf) * imvx;
   const double A13 = (sd * P.Cf * P.lf) * imvx + vy;
   const double A22 = -(P.Cr + P.Cf * cd) * imvx;
   const double A23 = -(P.lf * P.Cf * cd - P.lr * P.Cr) * imvx - vx;
   const double A32 = -(P.lf * P.Cf * cd - P.lr * P.Cr) * iIvx;
   const double A33 = -(P.lf * P.lf * P.Cf * cd + P.lr * P.lr * P.Cr) * iIvx;
-  const double B11 = -(sd * P.Cf) / P.m;
-  const double iden = 1.0 / (1.0 - ey * cur);
+  const double B11 = -(sd * P.Cf) * inv_m;
+  const double iden = q3_rcp(1.0 - ey * cur);
   const double dt = P.dt;
   // rows 0-2 of A_k = I + dt Ac, columns 1-2 (column 0 is (1 - dt mu, 0, 0))
   A[0] = dt * A12; A[1] = dt * A13;
@@ -54,8 +80,8 @@ __device__ __forceinline__ void sim_linearise(const DevParams& P, const double* 
   A[4] = dt * A32; A[5] = 1.0 + dt * A33;
   // B_k u_k: only the first three states have an input term
   A[6] = fma(dt * B11, delta, dt * acc);
-  A[7] = dt * ((cd * P.Cf) / P.m) * delta;
-  A[8] = dt * ((P.lf * P.Cf * cd) / P.I) * delta;
+  A[7] = dt * ((cd * P.Cf) * inv_m) * delta;
+  A[8] = dt * ((P.lf * P.Cf * cd) * inv_I) * delta;
   // integrator rows: e_y (vx, vy), e_psi (vx, vy; w has dt), s (vx, vy), x and y (vx, vy)
   A[9] = dt * se; A[10] = dt * ce;
   A[11] = dt * (iden * (-ce * cur)); A[12] = dt * (iden * (se * cur));
@@ -82,7 +108,7 @@ __global__ void __launch_bounds__(SIM_THREADS) lpv_sim_kernel(const __grid_const
   const double* gu = u + (size_t)b0 * N * 2;
   double* go = out + (size_t)b0 * rowd;
   const unsigned xbytes = (unsigned)nm * rowd * 8u, ubytes = (unsigned)nm * N * 16u;
-  // bulk copies need 16-byte aligned addresses and sizes (a full tile of 8 models always has them for aligned arrays)
+  // bulk copies need 16-byte aligned addresses and sizes (a full tile always has them for aligned arrays)
   const bool bulk = ((((size_t)gx | (size_t)gu | (size_t)go) & 15) == 0) && (xbytes & 15) == 0;
   if (tid < SIM_TILE) bad[tid] = 0;
 
@@ -108,15 +134,16 @@ __global__ void __launch_bounds__(SIM_THREADS) lpv_sim_kernel(const __grid_const
     __syncthreads();
   }
 
+  const double inv_m = 1.0 / P.m, inv_I = 1.0 / P.I;
   // ---- 2: one lane per (model, row): map lookup on every row, linearisation on rows 0 .. N-1
   for (int t = tid; t < nm * (N + 1); t += SIM_THREADS) {
     const int m = t / (N + 1), k = t - m * (N + 1);
     const double* x = tile + (size_t)t * NSTATE;
-    const int seg = map_segment(P, x[6]);
+    const int seg = sim_map_segment(P, x[6]);
     if (seg < 0) { bad[m] = 1; continue; }  // benign race: every writer stores 1
     if (k == N) continue;                   // row N: only the get_ey lookup
     const double2 uk = *(const double2*)(ut + ((size_t)m * N + k) * 2);
-    sim_linearise(P, x, uk.x, uk.y, P.seg_curv[seg], AB + (size_t)m * abm + (size_t)k * SIM_ABS);
+    sim_linearise(P, x, uk.x, uk.y, P.seg_curv[seg], AB + (size_t)m * abm + (size_t)k * SIM_ABS, inv_m, inv_I);
   }
   __syncthreads();
 

@@ -26,6 +26,7 @@
 #include "qp_types.h"
 
 #ifdef QP3_HOST
+struct Q3_V2 { double x, y; };
 #define Q3HD inline
 #define Q3D static inline
 #define Q3N static
@@ -42,6 +43,7 @@ static thread_local char* q3_host_smem = nullptr;
 #define Q3_SMEM q3_host_smem
 #else
 #include <cuda_runtime.h>
+typedef double2 Q3_V2;
 #define Q3HD __host__ __device__ inline
 #define Q3D __device__ __forceinline__
 #define Q3N __device__ __noinline__
@@ -148,13 +150,13 @@ Q3HD size_t carve_workspace3(Ctx3& c, char* sm, int N, int nn) {
   auto take = [&](size_t n) { double* r = p; p += n; return r; };
   const size_t n = (size_t)N, RT = (size_t)c.RT;
   c.Acol = take(Q3_AS * n); c.Bcol = take(4 * n);
+  c.F = take(18 * n); c.Wi = take(4 * n); c.zk = take(2 * n);  // even offsets, even strides: 128-bit loads per stage
   c.ax = take(n * nn); c.ay = take(n * nn); c.mx = take(n * nn); c.my = take(n * nn);
   c.eyb = take(n); c.pxy = take(2 * n);
   c.x = take(9 * n); c.u = take(2 * n); c.sig = take(3 * n); c.lam = take(RT); c.tt = take(RT);
   c.dx = take(9 * n); c.du = take(2 * n); c.dsig = take(3 * n); c.dlam = take(RT); c.dtt = take(RT);
   c.gx = c.dx; c.gu = c.du; c.gs = c.dsig;
   c.D = take(RT); c.res = take(RT);
-  c.F = take(18 * n); c.Wi = take(4 * n); c.zk = take(2 * n);
   c.Si = take(6 * n); c.bh = take(4 * n); c.Weff = take(10 * n);
   c.rinfo = (unsigned short*)take((RT + 3) / 4);
   c.act = (unsigned char*)take((RT + 7) / 8);
@@ -588,7 +590,8 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
     const double* A = c.Acol + Q3_AS * k;
     const double* B = c.Bcol + 4 * k;
     const double* d = hd->dbuf[k & 1];
-    const double B0 = B[0], B1 = B[1], B2 = B[2], B3 = B[3];
+    const Q3_V2 bA = ((const Q3_V2*)B)[0], bB = ((const Q3_V2*)B)[1];
+    const double B0 = bA.x, B1 = bA.y, B2 = bB.x, B3 = bB.y;
     // ---- phase 1
     Q3_PRED(l, 22) {
       const int r = l >> 1, h = l & 1;
@@ -706,9 +709,11 @@ Q3D void ric_affine_backward3(const Ctx3& c, double* ye, const int fb = 1) {
     const double* pvin = hd->pv[cur];
     const double* Fk = c.F + 18 * k;
     // what does not depend on the recursion first (the loads overlap the previous stage's barrier)
-    const double B0 = B[0], B1 = B[1], B2 = B[2], B3 = B[3];
+    const Q3_V2 bA = ((const Q3_V2*)B)[0], bB = ((const Q3_V2*)B)[1];
+    const Q3_V2 wA = ((const Q3_V2*)(c.Wi + 4 * k))[0], wB = ((const Q3_V2*)(c.Wi + 4 * k))[1];
+    const double B0 = bA.x, B1 = bA.y, B2 = bB.x, B3 = bB.y;
     const double gu0 = c.gu[2 * k], gu1 = c.gu[2 * k + 1];
-    const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
+    const double W00 = wA.x, W01 = wA.y, W11 = wB.x;
     const double hu0 = gu0 + pvin[0] + fma(B0, pin[0], fma(B1, pin[1], B2 * pin[2]));
     const double hu1 = gu1 + pvin[1] + B3 * pin[0];
     const double z0 = fb ? W00 * hu0 + W01 * hu1 : 0.0, z1 = fb ? W01 * hu0 + W11 * hu1 : 0.0;
@@ -748,26 +753,35 @@ Q3D void ric_affine_backward3(const Ctx3& c, double* ye, const int fb = 1) {
 Q3D void ric_forward3(const Ctx3& c, const int defects) {
   Hdr3* hd = c.hd;
   const double* dR2 = hd->dR2;
-  double* fx = hd->Y;        // the running stage's step (ping-pong 2 x 9, 2 x 2): over the backward sweeps' scratch
-  double* fu = hd->Y + 18;
-  Q3_ITEM(e, 9) fx[e] = 0.0;   // dx_0 = 0, dv_0 = 0: stage 0 runs the same code as the others
-  Q3_ITEM(e, 2) fu[e] = 0.0;
+  double* fx = hd->Y;        // the running stage's step (ping-pong 2 x 10 (9 used), 2 x 2): over the backward sweeps' scratch
+  double* fu = hd->Y + 20;
+  Q3_ITEM(e, 20) fx[e] = 0.0;  // dx_0 = 0, dv_0 = 0: stage 0 runs the same code as the others
+  Q3_ITEM(e, 4) fu[e] = 0.0;
   Q3_SYNC();
   int cur = 0;
 #pragma unroll 1
   for (int k = 0; k < c.N; ++k) {
     const double* A = c.Acol + Q3_AS * k;
-    const double* B = c.Bcol + 4 * k;
-    const double* Fk = c.F + 18 * k;
-    const double* xin = fx + 9 * cur;
-    const double* vin = fu + 2 * cur;
-    // what does not depend on the recursion first (the loads overlap the previous stage's barrier)
+    // what does not depend on the recursion first (the loads overlap the previous stage's barrier); 128-bit loads
     double f[18];
+    {
+      const Q3_V2* F2 = (const Q3_V2*)(c.F + 18 * k);
 #pragma unroll
-    for (int l = 0; l < 18; ++l) f[l] = Fk[l];
-    const double W00 = c.Wi[4 * k], W01 = c.Wi[4 * k + 1], W11 = c.Wi[4 * k + 2];
-    const double zk0 = c.zk[2 * k], zk1 = c.zk[2 * k + 1];
-    const double B0 = B[0], B1 = B[1], B2 = B[2], B3 = B[3];
+      for (int q = 0; q < 9; ++q) { const Q3_V2 t = F2[q]; f[2 * q] = t.x; f[2 * q + 1] = t.y; }
+    }
+    const Q3_V2 wA = ((const Q3_V2*)(c.Wi + 4 * k))[0], wB = ((const Q3_V2*)(c.Wi + 4 * k))[1];
+    const Q3_V2 zz = ((const Q3_V2*)(c.zk + 2 * k))[0];
+    const Q3_V2 bA = ((const Q3_V2*)(c.Bcol + 4 * k))[0], bB = ((const Q3_V2*)(c.Bcol + 4 * k))[1];
+    const double W00 = wA.x, W01 = wA.y, W11 = wB.x, zk0 = zz.x, zk1 = zz.y;
+    const double B0 = bA.x, B1 = bA.y, B2 = bB.x, B3 = bB.y;
+    double xin[10];
+    {
+      const Q3_V2* X2 = (const Q3_V2*)(fx + 10 * cur);
+#pragma unroll
+      for (int q = 0; q < 5; ++q) { const Q3_V2 t = X2[q]; xin[2 * q] = t.x; xin[2 * q + 1] = t.y; }
+    }
+    const Q3_V2 vv = ((const Q3_V2*)(fu + 2 * cur))[0];
+    const double vin[2] = {vv.x, vv.y};
     double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
 #pragma unroll
     for (int l = 0; l < 8; l += 2) {
@@ -782,10 +796,10 @@ Q3D void ric_forward3(const Ctx3& c, const int defects) {
       const double a0 = A[j * 3], a1 = A[j * 3 + 1], a2 = A[j * 3 + 2];
       const double dj = defects ? c.dlam[9 * k + j] : 0.0;
       const double bj0 = j == 0 ? B0 : (j == 1 ? B1 : (j == 2 ? B2 : 0.0)), bj1 = j == 0 ? B3 : 0.0;
-      double v = j >= 3 ? xin[j] : 0.0;
+      double v = j >= 3 ? fx[10 * cur + j] : 0.0;
       v = fma(a0, xin[0], v); v = fma(a1, xin[1], v); v = fma(a2, xin[2], v);
       v += fma(bj0, du0, bj1 * du1) + dj;
-      if (j_ok) { fx[9 * (cur ^ 1) + j] = v; c.dx[9 * k + j] = v; }
+      if (j_ok) { fx[10 * (cur ^ 1) + j] = v; c.dx[9 * k + j] = v; }
     }
     Q3_PREDS(l, 9, 11) {
       const double v = l == 9 ? du0 : du1;

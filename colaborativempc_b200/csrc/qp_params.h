@@ -37,4 +37,9 @@ static inline void fill_dev_params(const dmpc_params* p, const dmpc_options* o, 
   P.refine = o->polish_refine; P.pdas_first = o->pdas_first; P.pdas_after = o->pdas_after;
   P.ipm_max = o->ipm_max_iter;
   P.gr_global = 0; P.hk_global = 0;
+  P.seg_tiled = p->nseg >= 1;
+  for (int i = 0; i < p->nseg; ++i) {
+    if (!(p->seg_len[i] > 0.0)) P.seg_tiled = 0;
+    if (i + 1 < p->nseg && p->seg_s0[i + 1] != p->seg_s0[i] + p->seg_len[i]) P.seg_tiled = 0;
+  }
 }
