@@ -593,6 +593,37 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
     const Q3_V2 bA = ((const Q3_V2*)B)[0], bB = ((const Q3_V2*)B)[1];
     const double B0 = bA.x, B1 = bA.y, B2 = bB.x, B3 = bB.y;
     // ---- phase 1
+#if !defined(QP3_HOST) && defined(Q3_DMMA)
+    // A/B variant (tensor cores): [Y | Yb] = Pf (11 x 9) [Acol | d | b0 | b1] (9 x 6) as six DMMA m8n8k4
+    // (two row tiles x three k steps) instead of 18 FMAs on 22 lanes
+    {
+      const int lane = Q3_LANE, g = lane >> 2, t = lane & 3;
+      double c00 = 0.0, c01 = 0.0, c10 = 0.0, c11 = 0.0;
+#pragma unroll
+      for (int sK = 0; sK < 3; ++sK) {
+        const int kk = 4 * sK + t;
+        const int kc = kk < 9 ? kk : 8;
+        const double bv_a = A[3 * kc + (g < 3 ? g : 0)], bv_d = d[kc], bv_b = B[kc < 3 ? kc : 0];
+        double bv = g < 3 ? bv_a : (g == 3 ? bv_d : (g == 4 ? (kk < 3 ? bv_b : 0.0) : ((g == 5 && kk == 0) ? B3 : 0.0)));
+        bv = kk < 9 ? bv : 0.0;
+        const double a0v = Pf[g * 9 + kc];
+        const double a1v = Pf[(g < 3 ? 8 + g : 8) * 9 + kc];
+        const double av0 = kk < 9 ? a0v : 0.0, av1 = (kk < 9 && g < 3) ? a1v : 0.0;
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c00), "+d"(c01) : "d"(av0), "d"(bv));
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c10), "+d"(c11) : "d"(av1), "d"(bv));
+      }
+      // C fragment: rows g (tile 0) and 8 + g (tile 1), columns 2t, 2t + 1: t = 0, 1 -> Y, t = 2 -> Yb
+      const double px0 = px[g], px1 = px[8];
+      if (t < 2) {
+        hd->Y[g * 4 + 2 * t] = c00; hd->Y[g * 4 + 2 * t + 1] = c01;
+        if (g < 3) { hd->Y[(8 + g) * 4 + 2 * t] = c10; hd->Y[(8 + g) * 4 + 2 * t + 1] = c11; }
+        if (t == 1) { hd->pe[g] = px0 + c01; if (g == 0) hd->pe[8] = px1 + c11; }
+      } else if (t == 2) {
+        hd->Yb[g * 2] = c00; hd->Yb[g * 2 + 1] = c01;
+        if (g < 3) { hd->Yb[(8 + g) * 2] = c10; hd->Yb[(8 + g) * 2 + 1] = c11; }
+      }
+    }
+#else
     Q3_PRED(l, 22) {
       const int r = l >> 1, h = l & 1;
       double p[9];
@@ -618,6 +649,7 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
         if (h && r < 9) hd->pe[r] = pxe;
       }
     }
+#endif
     Q3_SYNC();
     // ---- phase 2: scalar section, identical on every lane
     const double* Yb = hd->Yb;
