@@ -14,6 +14,80 @@
 // loose thresholds that decide "the guess is clearly wrong, do not spend refinement passes on it"
 #define Q3_LOOSE 1e-6
 
+// One pass of the method of multipliers, ONE LANE PER STAGE and straight-line per row (no row decoding): the residuals of
+// the stage's rows at the current iterate (as eval_residuals3), lam += D res, and the pass statistics: v = how far the
+// active rows are from their bounds (relative), lm = max |lam|, dl = max |D res| (the multiplier update), bad = non-finite.
+// All lanes return the reduced values.  Ends with a barrier.
+Q3D int pass_update3(const Ctx3& c, double& v_out, double& lm_out, double& dl_out) {
+  const double* lim = c.hd->lim;
+  const double hm = 0.5 * c.hd->mind;
+  double v = 0.0, lm = 0.0, dl = 0.0;
+  int bad = 0;
+  auto row = [&](int j, double res, double babs) {
+    const double D = c.D[j];
+    const double dr = D * res, l = c.lam[j] + dr;
+    c.res[j] = res; c.lam[j] = l;
+    dl = fmax(dl, fabs(dr)); lm = fmax(lm, fabs(l));
+    if (!(fabs(res) < 1e300) || !(fabs(l) < 1e300)) bad = 1;
+    if (D > 0.0) v = fmax(v, fabs(res) / (1.0 + babs));
+  };
+  Q3_FOR(k, c.N) {
+    const double* xk = c.x + 9 * k;
+    const double* sk = c.sig + 3 * k;
+    const int j0 = k * c.rst, jb = c.Rs + 4 * k;
+    const double eb = c.eyb[k];
+    row(j0, lim[0] - xk[0], fabs(lim[0]));
+    row(j0 + 1, (xk[0] - lim[1]) + sk[0], fabs(lim[1]));
+    row(j0 + 2, (xk[3] - eb) + sk[1], fabs(eb));
+    row(j0 + 3, (-xk[3] - eb) + sk[1], fabs(eb));
+#pragma unroll 1
+    for (int i = 0; i < c.nn; ++i) {
+      const int q = k * c.nn + i;
+      if (i < c.cnt) {
+        const double ax = c.ax[q], ay = c.ay[q], mx = c.mx[q], my = c.my[q];
+        row(j0 + 4 + i, fma(ax, xk[7] - mx, ay * (xk[8] - my)) + (hm - sk[2]), fabs(fma(ax, mx, ay * my) - hm));
+      } else {
+        c.res[j0 + 4 + i] = -1.0;
+      }
+    }
+    const double u0 = c.u[2 * k], u1 = c.u[2 * k + 1];
+    row(jb, u0 - lim[2], fabs(lim[2])); row(jb + 1, -u0 - lim[3], fabs(lim[3]));
+    row(jb + 2, u1 - lim[4], fabs(lim[4])); row(jb + 3, -u1 - lim[5], fabs(lim[5]));
+  }
+  bad = q3_wor(bad);
+  v_out = q3_wmax(v); lm_out = q3_wmax(lm); dl_out = q3_wmax(dl);
+  Q3_SYNC();
+  return bad;
+}
+
+// Judging / updating the guess, one lane per stage: a row outside the guess that is violated beyond tol (relative to
+// 1 + |b|) or a row inside it whose multiplier is below -tol lm.  update = 0: returns whether any row would move;
+// update = 1: moves them (c.act) and ends with a barrier.
+Q3D int judge_rows3(const Ctx3& c, double tol, double lm, int update) {
+  const double* lim = c.hd->lim;
+  const double hm = 0.5 * c.hd->mind;
+  int changed = 0;
+  auto row = [&](int j, double babs) {
+    const int a = c.act[j];
+    const bool mv = a ? (c.lam[j] < -tol * lm) : (c.res[j] > tol * (1.0 + babs));
+    if (mv) { changed = 1; if (update) c.act[j] = (unsigned char)(a ? 0 : 1); }
+  };
+  Q3_FOR(k, c.N) {
+    const int j0 = k * c.rst, jb = c.Rs + 4 * k;
+    const double eb = fabs(c.eyb[k]);
+    row(j0, fabs(lim[0])); row(j0 + 1, fabs(lim[1])); row(j0 + 2, eb); row(j0 + 3, eb);
+#pragma unroll 1
+    for (int i = 0; i < c.cnt; ++i) {
+      const int q = k * c.nn + i;
+      row(j0 + 4 + i, fabs(fma(c.ax[q], c.mx[q], c.ay[q] * c.my[q]) - hm));
+    }
+    row(jb, fabs(lim[2])); row(jb + 1, fabs(lim[3])); row(jb + 2, fabs(lim[4])); row(jb + 3, fabs(lim[5]));
+  }
+  changed = q3_wor(changed);
+  if (update) Q3_SYNC();
+  return changed;
+}
+
 // One active-set round on c.act.  first: the iterate is the bounded starting point, not yet dynamics-consistent.
 // Returns 1 certified, 0 guess updated (c.act), 2 numerical failure (non-finite).
 // On exit c.x, c.u, c.sig, c.lam, c.res belong to the guess that was solved.
@@ -40,23 +114,10 @@ Q3N int polish_round3(int first) {
   double v_prev = 1e300;
 #pragma unroll 1
   for (;;) {
-    eval_residuals3(c);
-    // multiplier update, then: how far are the active rows from their bounds, is the guess still plausible
-    double v = 0.0, lm = 0.0, dl = 0.0;
-    int bad = 0;
-    Q3_FOR(j, c.RT) {
-      const double l = fma(c.D[j], c.res[j], c.lam[j]);
-      dl = fmax(dl, fabs(c.D[j] * c.res[j]));
-      c.lam[j] = l;
-      if (!(fabs(c.res[j]) < 1e300) || !(fabs(l) < 1e300)) bad = 1;
-      lm = fmax(lm, fabs(l));
-      if (c.D[j] > 0.0) v = fmax(v, fabs(c.res[j]) / (1.0 + fabs(row_b3(c, j))));
-    }
-    if (q3_wor(bad)) return 2;
-    lm = 1.0 + q3_wmax(lm);
-    v = q3_wmax(v);
-    dl = q3_wmax(dl);
-    Q3_SYNC();
+    // residuals, multiplier update, then: how far are the active rows from their bounds, is the guess still plausible
+    double v, lm, dl;
+    if (pass_update3(c, v, lm, dl)) return 2;
+    lm = 1.0 + lm;
 #ifdef QP3_TRACE
     { double dl = 0; for (int j = 0; j < c.RT; ++j) dl = fmax(dl, fabs(c.D[j] * c.res[j])); int na = 0; for (int j = 0; j < c.RT; ++j) na += c.act[j];
       printf("  pass %d v %.3e dlam %.3e lm %.3e nact %d\n", pass, v, dl, lm, na); }
@@ -76,24 +137,11 @@ Q3N int polish_round3(int first) {
     // ... and while the active rows are still far from their bounds (multipliers of 1e7 and more leave them 1e-2 off
     // after the first pass) neither the other rows' residuals nor the multipliers' signs mean anything yet: refine first
     const bool judge = tight || v <= 1e-4 || last;
-    int changed = 0;
-    if (judge) {
-      Q3_FOR(j, c.RT) {
-        if (!row_ok3(c, j)) continue;
-        if (!c.act[j]) { if (c.res[j] > tol * (1.0 + fabs(row_b3(c, j)))) changed = 1; }
-        else if (c.lam[j] < -tol * lm) changed = 1;
-      }
-    }
-    changed = q3_wor(changed);
+    const int changed = judge ? judge_rows3(c, tol, lm, 0) : 0;
     if (tight && !changed) return 1;
     if (changed || last) {
       // update the guess with the tight thresholds (a row the loose test let through still moves)
-      Q3_FOR(j, c.RT) {
-        if (!row_ok3(c, j)) continue;
-        if (!c.act[j]) { if (c.res[j] > cert_tol * (1.0 + fabs(row_b3(c, j)))) c.act[j] = 1; }
-        else if (c.lam[j] < -cert_tol * lm) c.act[j] = 0;
-      }
-      Q3_SYNC();
+      judge_rows3(c, cert_tol, lm, 1);
       return 0;
     }
     affine_solve3(G3_ALM, 0.0);
