@@ -217,6 +217,75 @@ Q3D void ipm_park3(const Ctx3& c, double* park, int save) {
   Q3_SYNC();
 }
 
+// Top of an interior-point iteration, ONE LANE PER STAGE (straight-line per row, no row decoding): the residuals at the
+// iterate (as eval_residuals3), the per-lane partial sums of the complementarity lam't, the primal residual |res + t| and the
+// largest multiplier, and the weights D = lam / t of the next factorisation.  Unused neighbour rows are inert by
+// construction (lam = 0, t = 1, res = -1, steps 0), so the flat loops of the iteration need no validity test.  Ends with
+// a barrier.
+Q3D void ipm_rows_eval3(const Ctx3& c, double& v_mu, double& v_rp, double& v_lm) {
+  const double* lim = c.hd->lim;
+  const double hm = 0.5 * c.hd->mind;
+  auto row = [&](int j, double res) {
+    const double t = c.tt[j], l = c.lam[j];
+    c.res[j] = res;
+    v_mu = fma(l, t, v_mu); v_rp = fmax(v_rp, fabs(res + t)); v_lm = fmax(v_lm, l);
+    c.D[j] = l * q3_rcp(t);
+  };
+  Q3_FOR(k, c.N) {
+    const double* xk = c.x + 9 * k;
+    const double* sk = c.sig + 3 * k;
+    const int j0 = k * c.rst, jb = c.Rs + 4 * k;
+    const double eb = c.eyb[k];
+    row(j0, lim[0] - xk[0]);
+    row(j0 + 1, (xk[0] - lim[1]) + sk[0]);
+    row(j0 + 2, (xk[3] - eb) + sk[1]);
+    row(j0 + 3, (-xk[3] - eb) + sk[1]);
+#pragma unroll 1
+    for (int i = 0; i < c.nn; ++i) {
+      const int q = k * c.nn + i;
+      if (i < c.cnt) row(j0 + 4 + i, fma(c.ax[q], xk[7] - c.mx[q], c.ay[q] * (xk[8] - c.my[q])) + (hm - sk[2]));
+      else { c.res[j0 + 4 + i] = -1.0; c.D[j0 + 4 + i] = 0.0; }
+    }
+    const double u0 = c.u[2 * k], u1 = c.u[2 * k + 1];
+    row(jb, u0 - lim[2]); row(jb + 1, -u0 - lim[3]); row(jb + 2, u1 - lim[4]); row(jb + 3, -u1 - lim[5]);
+  }
+  Q3_SYNC();
+}
+
+// Slack and multiplier steps from the primal direction, one lane per stage:  dt = -(res + t) - (A d)_j;  predictor
+// dlam = -(lam + D dt);  corrector dlam = -(lam t + dt_aff dlam_aff - smu + lam dt) / t  (c.dtt / c.dlam hold the affine
+// step on entry).  Returns the largest step in (0, 1] that keeps t and lam non-negative (all lanes).  Ends with a barrier.
+Q3D double ipm_row_steps3(const Ctx3& c, const int corrector, const double smu) {
+  double a = 1.0;
+  auto row = [&](int j, double av) {
+    const double t = c.tt[j], l = c.lam[j];
+    const double dt = -(c.res[j] + t) - av;
+    double dl;
+    if (corrector) dl = -((fma(c.dtt[j], c.dlam[j], l * t) - smu) + l * dt) * q3_rcp(t);
+    else dl = -(l + c.D[j] * dt);
+    c.dtt[j] = dt; c.dlam[j] = dl;
+    if (fma(a, dt, t) < 0.0) a = -t / dt;   // dt < 0 and -t / dt < a
+    if (fma(a, dl, l) < 0.0) a = -l / dl;
+  };
+  Q3_FOR(k, c.N) {
+    const double* dk = c.dx + 9 * k;
+    const double* sk = c.dsig + 3 * k;
+    const int j0 = k * c.rst, jb = c.Rs + 4 * k;
+    row(j0, -dk[0]); row(j0 + 1, dk[0] + sk[0]); row(j0 + 2, dk[3] + sk[1]); row(j0 + 3, -dk[3] + sk[1]);
+#pragma unroll 1
+    for (int i = 0; i < c.nn; ++i) {
+      const int q = k * c.nn + i;
+      if (i < c.cnt) row(j0 + 4 + i, c.ax[q] * dk[7] + c.ay[q] * dk[8] - sk[2]);
+      else { c.dtt[j0 + 4 + i] = 0.0; c.dlam[j0 + 4 + i] = 0.0; }
+    }
+    const double d0 = c.du[2 * k], d1 = c.du[2 * k + 1];
+    row(jb, d0); row(jb + 1, -d0); row(jb + 2, d1); row(jb + 3, -d1);
+  }
+  a = q3_wmin(a);
+  Q3_SYNC();
+  return a;
+}
+
 // Mehrotra predictor-corrector down to complementarity mu_tol.  warm: continue from the parked iterate.
 // One step length for primal and dual (the Hessian couples them): every linear residual - dual, primal, dynamics -
 // then contracts by exactly (1 - alpha) per iteration, which is how the dual residual is tracked (its costates are
@@ -264,10 +333,8 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
   double gmax = 1.0 + fabs(hd->q0);
 #pragma unroll 1
   for (int it = 0; it < ipm_max; ++it) {
-    eval_residuals3(c);
     double v_mu = 0.0, v_rp = 0.0, v_lm = 0.0;
-    Q3_FOR(j, c.RT)
-      if (row_ok3(c, j)) { v_mu = fma(c.lam[j], c.tt[j], v_mu); v_rp = fmax(v_rp, fabs(c.res[j] + c.tt[j])); v_lm = fmax(v_lm, c.lam[j]); }
+    ipm_rows_eval3(c, v_mu, v_rp, v_lm);
     double v_obj = 0.0;
     Q3_FOR(k, c.N) {  // scale of the objective (the exact value is computed by the epilogue)
       const double* xk = c.x + 9 * k;
@@ -283,34 +350,16 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     if (!isfinite(mu) || !isfinite(rp)) return 3;
     if (!(mu < 1e40) || !(rp < 1e40)) return 1;
     if (mu <= mu_tol * (1.0 + obj) && rp <= 10.0 * mu_tol && rd <= 10.0 * mu_tol * (gmax + lmax)) return 0;
-    // ---- predictor (factorisation for D = lam / t)
-    Q3_FOR(j, c.RT) c.D[j] = row_ok3(c, j) ? c.lam[j] / c.tt[j] : 0.0;
-    Q3_SYNC();
+    // ---- predictor (factorisation for D = lam / t, set by ipm_rows_eval3)
     factor_solve3(G3_AFF, 0);
-    Q3_FOR(j, c.RT) {
-      if (!row_ok3(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
-      const double dt = -(c.res[j] + c.tt[j]) - row_val3(c, j, c.dx, c.dsig, c.du);
-      c.dtt[j] = dt;
-      c.dlam[j] = -(c.lam[j] + c.D[j] * dt);
-    }
-    Q3_SYNC();
-    const double aa = fmin(step_to_boundary3(c, c.tt, c.dtt), step_to_boundary3(c, c.lam, c.dlam));
+    const double aa = ipm_row_steps3(c, 0, 0.0);
     double v_aff = 0.0;
-    Q3_FOR(j, c.RT)
-      if (row_ok3(c, j)) v_aff = fma(c.lam[j] + aa * c.dlam[j], c.tt[j] + aa * c.dtt[j], v_aff);
+    Q3_FOR(j, c.RT) v_aff = fma(c.lam[j] + aa * c.dlam[j], c.tt[j] + aa * c.dtt[j], v_aff);
     const double mu_aff = q3_wsum(v_aff) / m;
     const double sr = mu_aff / mu, smu = sr * sr * sr * mu;
     // ---- corrector: same factor, full right-hand side with the second-order term (smu - dt_aff dlam_aff) / t
     affine_solve3(G3_COR, smu);
-    Q3_FOR(j, c.RT) {
-      if (!row_ok3(c, j)) { c.dtt[j] = 0.0; c.dlam[j] = 0.0; continue; }
-      const double dt = -(c.res[j] + c.tt[j]) - row_val3(c, j, c.dx, c.dsig, c.du);
-      const double rc = c.lam[j] * c.tt[j] + c.dtt[j] * c.dlam[j] - smu;
-      c.dtt[j] = dt;
-      c.dlam[j] = -(rc + c.lam[j] * dt) / c.tt[j];
-    }
-    Q3_SYNC();
-    const double al = fmin(1.0, 0.99 * fmin(step_to_boundary3(c, c.tt, c.dtt), step_to_boundary3(c, c.lam, c.dlam)));
+    const double al = fmin(1.0, 0.99 * ipm_row_steps3(c, 1, smu));
 #ifdef QP3_TRACE3
     printf("  ipm it %d mu %.3e rp %.3e lin %.2e aa %.3f sig %.3f al %.4f lmax %.2e\n", it, mu, rp, lin, aa, sr*sr*sr, al, lmax);
 #endif
