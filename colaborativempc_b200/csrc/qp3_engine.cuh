@@ -71,22 +71,16 @@ __device__ __forceinline__ unsigned long long q3_wsum64(unsigned long long v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
-// 1 / d without the slow-path branch of the division: d = m 2^e, single-precision seed for 1 / m, three Newton steps (the
-// last in residual form: relative error about one ulp), exponent put back by integer arithmetic - safe over the whole
-// range a 2 x 2 determinant with interior-point weights lam / t can take (1e38 and beyond).  Non-finite or zero d gives NaN.
+// 1 / d without the slow-path branch of the division: the hardware's double-precision reciprocal seed (MUFU.RCP64H,
+// about 20 bits, full exponent range) and three Newton steps, the last in residual form: relative error about one ulp.
+// Zero, infinite and non-finite d give NaN (the callers' finiteness checks see them).
 __device__ __forceinline__ double q3_rcp(double d) {
-  const int hi = __double2hiint(d), lo = __double2loint(d);
-  const int e = (hi >> 20) & 0x7ff;
-  const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, lo);  // [1, 2)
-  double x = (double)__frcp_rn((float)m);
-  x = x * fma(-m, x, 2.0);
-  x = x * fma(-m, x, 2.0);
-  x = fma(x, fma(-m, x, 1.0), x);
-  const int xh = (__double2hiint(x) - ((e - 1023) << 20)) | (hi & 0x80000000);
-  const double res = __hiloint2double(xh, __double2loint(x));
-  return (e == 0 || e == 0x7ff) ? __longlong_as_double(0x7ff8000000000000LL) : res;
+  double x;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(d));
+  x = x * fma(-d, x, 2.0);
+  x = x * fma(-d, x, 2.0);
+  return fma(x, fma(-d, x, 1.0), x);
 }
-
 extern __shared__ __align__(16) char smem_stage[];
 #define Q3_SMEM smem_stage
 #endif
