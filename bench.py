@@ -341,6 +341,10 @@ def run_single(args):
     n_one = torch.zeros((), dtype=torch.int64, device=dev)
     it_sum = torch.zeros((), dtype=torch.float64, device=dev)
     rd_sum = torch.zeros((), dtype=torch.float64, device=dev)
+    # hard-QP hint (the one-bit "ended in the interior point last step" carried with the launch order): how well does the
+    # previous, different batch predict this one?  Counted on the device, read after the timed loop.
+    prev_hard = torch.zeros((BATCH,), dtype=torch.bool, device=dev)
+    hint_cnt = torch.zeros((4,), dtype=torch.int64, device=dev)  # hard now, hard now & hinted, hinted, hinted & not hard now
     sampler = ClockSampler(local)
     pairs, e2e_s, bad_h = [], [], 0
     for i in range(nb):
@@ -361,6 +365,9 @@ def run_single(args):
             n_one += (d_out["status"] == 1).sum()
             it_sum += d_out["iters"].double().sum()
             rd_sum += d_out["pivots"].double().sum()
+            hard = d_out["iters"] > 0
+            hint_cnt += torch.stack([hard.sum(), (hard & prev_hard).sum(), prev_hard.sum(), (prev_hard & ~hard).sum()])
+        prev_hard = d_out["iters"] > 0
         # the same batch end to end through the host-buffer C-ABI call, on the same iteration
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -427,6 +434,11 @@ def run_single(args):
             "p50_step_ms": float(np.median(per_step)), "wall_ms_per_step": 1e3 * t_wall / args.steps,
             "solved": solved, "qp_timed": qp_timed, "solved_inaccurate": qp_timed - solved - int(n_bad.item()), "infeasible": infeasible,
             "ipm_iters_mean": float(it_sum.item()) / qp_timed, "polish_rounds_mean": float(rd_sum.item()) / qp_timed, "sweep": sweep}
+    hc = [int(v) for v in hint_cnt.tolist()]
+    line["hint"] = {"interior_point_qps": hc[0], "of_them_hinted": hc[1], "hit_rate": hc[1] / max(hc[0], 1), "hinted_qps": hc[2],
+                    "hinted_but_certified_by_rounds": hc[3], "share_of_batch": hc[0] / qp_timed,
+                    "what": "live stream: a QP is hinted when the QP of the same index in the PREVIOUS (different) batch ended in the "
+                            "interior point; hit_rate = interior-point QPs of a step that were hinted (started first, one round only)"}
     print(json.dumps(line))
     if infeasible:
         sys.stderr.write("FAIL: %d QPs of the timed steps did not come back feasible\n" % infeasible)

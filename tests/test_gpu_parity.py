@@ -605,6 +605,15 @@ def test_model_rollout_vs_reference_and_oracle(built, cfg, track):
     out, st = eng.sim_batch(dev(xp), dev(u))
     assert np.array_equal(st.cpu().numpy(), rst) and np.all(rst == 0)
     assert np.abs(out.cpu().numpy() - ref).max() <= 1e-12 * (1 + np.abs(ref).max())
+    # (2b) the tile paths of the kernel: a ragged last tile whose byte range is not a multiple of 16 (plain loads / stores
+    # instead of the bulk copies) and caller pointers that are only 8-byte aligned (a view starting at model 1)
+    full = out.cpu().numpy()
+    xd, ud = dev(xp), dev(u)
+    out, st = eng.sim_batch(xd[:1021], ud[:1021])
+    assert np.all(st.cpu().numpy() == 0) and np.array_equal(out.cpu().numpy(), full[:1021])
+    out, st = eng.sim_batch(xd[1:1000], ud[1:1000])
+    assert xd[1:].data_ptr() % 16 == 8
+    assert np.all(st.cpu().numpy() == 0) and np.array_equal(out.cpu().numpy(), full[1:1000])
     # (3) drop-in class, chained calls
     m = LPV_Model(N, cfg["dt"], track, model_param=cfg["model_param"], sys_lim=cfg["sys_lim"])
     m.xPred = g["xpred"][0].copy()
