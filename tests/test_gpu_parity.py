@@ -392,6 +392,47 @@ def test_edge_cases(built, cfg, track):
     assert np.all(yi[:, 4:] == 0)
 
 
+def test_input_staging_is_alignment_independent(built, cfg, track):
+    """The stage-wise kernel stages the per-QP inputs in shared memory with bulk async copies (TMA) of the 16-byte aligned
+    interior of each array and plain loads of an odd head / tail double.  Every alignment class must give the same bits:
+    caller pointers that are only 8-byte aligned (views starting one double into a buffer), Last_xPredicted with N and
+    with N+1 rows (72-byte rows: with 21 of them odd QPs start 8 bytes off), a single QP."""
+    import torch
+    fx = golden("platoon_N20.npz")
+    eng = _engine(cfg, track, options={"warm_start": 0, "order_hint": 0})  # bit-for-bit: nothing carried between calls
+    ins = {k: np.ascontiguousarray(fx["it3_%s" % k]) for k in INPUT_KEYS}
+    assert ins["xprev"].shape[1] == 20
+
+    def dev_off(a, off):
+        flat = torch.empty(a.size + off, dtype=torch.float64 if a.dtype == np.float64 else torch.int32, device="cuda")
+        v = flat[off:].view(*a.shape)
+        v.copy_(torch.from_numpy(a))
+        return v
+
+    def run(d, off):
+        return eng.solve_batch(**{k: dev_off(v, off if v.dtype == np.float64 else 0) for k, v in d.items()})
+
+    ref = {k: v.cpu().numpy() for k, v in run(ins, 0).items()}
+    assert np.all(ref["status"] == 1)
+    keys = ("z", "y_ineq", "y_eq", "obj", "planes", "status")
+    for off in (1, 3):
+        d = {k: dev_off(v, off if v.dtype == np.float64 else 0) for k, v in ins.items()}
+        assert d["xprev"].data_ptr() % 16 == 8 and d["pose"].data_ptr() % 16 == 8
+        out = eng.solve_batch(**d)
+        for k in keys:
+            assert np.array_equal(out[k].cpu().numpy(), ref[k]), (off, k)
+    # N + 1 rows (the extra row only adds its track lookup): 1512-byte slices, every odd QP starts 8 bytes off
+    ins21 = dict(ins, xprev=np.ascontiguousarray(np.concatenate([ins["xprev"], ins["xprev"][:, -1:]], axis=1)))
+    for off in (0, 1):
+        out = run(ins21, off)
+        for k in keys:
+            assert np.array_equal(out[k].cpu().numpy(), ref[k]), ("21 rows", off, k)
+    # one QP alone, from an odd position
+    one = {k: np.ascontiguousarray(v[5:6]) for k, v in ins21.items()}
+    o = run(one, 1)
+    assert np.array_equal(o["z"].cpu().numpy()[0], ref["z"][5]) and np.array_equal(o["y_eq"].cpu().numpy()[0], ref["y_eq"][5])
+
+
 def test_full_size_batch_properties(built, cfg, track):
     """BASELINE config 2 at full size (4096 scenario QPs): all certified, batch-position independent (bitwise),
     replicas identical, objective = 1/2 z'Pz + q'z recomputed on the host."""
