@@ -306,13 +306,18 @@ Q3D int setup_planes3(const Ctx3& c, const DevParams& P, const double* nbr, cons
       c.ax[h * c.nn + n] = ax; c.ay[h * c.nn + n] = ay;
       c.mx[h * c.nn + n] = n < c.cnt ? 0.5 * (ex + nbr[(h * c.nn + n) * 2]) : 0.0;
       c.my[h * c.nn + n] = n < c.cnt ? 0.5 * (ey + nbr[(h * c.nn + n) * 2 + 1]) : 0.0;
-      if (planes_out) {
-        planes_out[(h * 3 + 0) * c.nn + n] = ax;
-        planes_out[(h * 3 + 1) * c.nn + n] = ay;
-        planes_out[(h * 3 + 2) * c.nn + n] = bb;
-      }
+      if (planes_out) c.res[h * c.nn + n] = bb;  // offsets parked for the coalesced write below (res is not live yet)
     }
     c.pxy[2 * h] = P.wq * sx; c.pxy[2 * h + 1] = P.wq * sy;
+  }
+  if (planes_out) {  // planes (N, 3, nn) written as consecutive doubles: full lines, not 8-byte fragments 48 bytes apart
+    Q3_SYNC();
+    const int per = 3 * c.nn;
+    Q3_FOR(i, c.N * per) {
+      const int h = i / per, rem = i - h * per, cc = rem / c.nn, n = rem - cc * c.nn;
+      const int q = h * c.nn + n;
+      planes_out[i] = cc == 0 ? c.ax[q] : (cc == 1 ? c.ay[q] : c.res[q]);
+    }
   }
   return bad;
 }
