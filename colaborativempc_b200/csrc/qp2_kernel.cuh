@@ -312,44 +312,57 @@ __device__ __forceinline__ int cost_class(int cst) {
 
 __global__ void __launch_bounds__(ORDER_THREADS, 1) order_by_cost_kernel(const int* __restrict__ cost, int* __restrict__ order,
                                                                          int* __restrict__ nhard, int B, int nsm) {
-  __shared__ int wsum[ORDER_THREADS / 32];
-  __shared__ int base;
+  // One pass: every thread counts its chunk into the eight classes, ONE block-wide scan of the eight counters (two
+  // barriers instead of four per class), then the scatter.  Same order as a class-by-class counting sort.
+  __shared__ int wsum[ORDER_THREADS / 32][ORDER_CLASSES];  // inclusive per-warp totals, then their scan over the warps
   const int chunk = (B + ORDER_THREADS - 1) / ORDER_THREADS;
   const int lo = min(B, (int)threadIdx.x * chunk), hi = min(B, lo + chunk);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) base = 0;
-  __syncthreads();
-#pragma unroll 1
-  for (int cls = ORDER_CLASSES - 1; cls >= 0; --cls) {
-    int mine = 0;
-    for (int i = lo; i < hi; ++i) mine += (cost_class(cost[i]) == cls);
-    int incl = mine;  // inclusive scan over the block
+  int mine[ORDER_CLASSES], incl[ORDER_CLASSES];
+#pragma unroll
+  for (int c = 0; c < ORDER_CLASSES; ++c) mine[c] = 0;
+  for (int i = lo; i < hi; ++i) {
+    const int cl = cost_class(cost[i]);
+#pragma unroll
+    for (int c = 0; c < ORDER_CLASSES; ++c) mine[c] += (cl == c);
+  }
+#pragma unroll
+  for (int c = 0; c < ORDER_CLASSES; ++c) {
+    int v = mine[c];
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
+      const int w = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += w;
     }
-    if (lane == 31) wsum[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-      int v = wsum[lane];
+    incl[c] = v;
+    if (lane == 31) wsum[warp][c] = v;
+  }
+  __syncthreads();
+  if (warp < ORDER_CLASSES) {  // warp c scans class c over the 32 warps
+    int v = wsum[lane][warp];
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int w = __shfl_up_sync(0xffffffffu, v, o);
-        if (lane >= o) v += w;
-      }
-      wsum[lane] = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int w = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += w;
     }
-    __syncthreads();
-    int pos = base + incl - mine + (warp ? wsum[warp - 1] : 0);
-    for (int i = lo; i < hi; ++i)
-      if (cost_class(cost[i]) == cls) order[pos++] = i;
-    const int total = wsum[ORDER_THREADS / 32 - 1];
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      base += total;
-      if (cls == 6) *nhard = min(base, nsm);  // classes 7 and 6: at least one interior-point iteration
-    }
-    __syncthreads();
+    wsum[lane][warp] = v;
+  }
+  __syncthreads();
+  // most expensive class first: where class c starts = the totals of the classes above it
+  int pos[ORDER_CLASSES];
+  int base = 0;
+#pragma unroll
+  for (int c = ORDER_CLASSES - 1; c >= 0; --c) {
+    pos[c] = base + incl[c] - mine[c] + (warp ? wsum[warp - 1][c] : 0);
+    base += wsum[ORDER_THREADS / 32 - 1][c];
+    if (c == 6 && threadIdx.x == 0) *nhard = min(base, nsm);  // classes 7 and 6: at least one interior-point iteration
+  }
+  for (int i = lo; i < hi; ++i) {
+    const int cl = cost_class(cost[i]);
+    int p = 0;
+#pragma unroll
+    for (int c = 0; c < ORDER_CLASSES; ++c)
+      if (cl == c) { p = pos[c]; pos[c] = p + 1; }
+    order[p] = i;
   }
 }
