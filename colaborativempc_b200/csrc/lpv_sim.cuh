@@ -194,3 +194,4 @@ __global__ void __launch_bounds__(SIM_THREADS) lpv_sim_kernel(const __grid_const
     for (int i = tid; i < nm * rowd; i += SIM_THREADS) go[i] = tile[i];
   }
 }
+

@@ -39,7 +39,7 @@ static inline void fill_dev_params(const dmpc_params* p, const dmpc_options* o, 
   P.gr_global = 0; P.hk_global = 0;
   P.seg_tiled = p->nseg >= 1;
   for (int i = 0; i < p->nseg; ++i) {
-    if (!(p->seg_len[i] > 0.0)) P.seg_tiled = 0;
+    if (!(p->seg_len[i] >= 0.0)) P.seg_tiled = 0;  // zero-length segments (the reference's tracks start and end with one) never match and are skipped
     if (i + 1 < p->nseg && p->seg_s0[i + 1] != p->seg_s0[i] + p->seg_len[i]) P.seg_tiled = 0;
   }
 }

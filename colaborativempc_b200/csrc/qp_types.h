@@ -28,7 +28,7 @@ struct DevParams {
   int pdas_after;           // active-set rounds after each interior-point phase
   int ipm_max;              // interior-point iteration cap per phase
   int gr_global, hk_global; // 1: prediction rows / Hessian+factor live in the global workspace (long horizons)
-  int seg_tiled;            // 1: the track segments tile [s0[0], end) exactly (s0[i+1] == s0[i] + len[i], len > 0): one compare per segment finds the only match
+  int seg_tiled;            // 1: the track segments tile [s0[0], end) exactly (s0[i+1] == s0[i] + len[i], len >= 0): one compare per segment finds the only match
 };
 
 struct BatchPtrs {
