@@ -513,11 +513,11 @@ def run_dmpc(args):
 
     made = []   # every ShardedDMPC of this run: their graphs are released before the process group is torn down
 
-    def make(S, A, w, r, topo="chain", nn=NN, seed0=0):
+    def make(S, A, w, r, topo="chain", nn=NN, seed0=0, group=None):
         eng = BatchedPlannerLPV(*planner_args(cfg, track, HORIZON), nn=nn, max_batch=S * A // w, options=opts)
         x0, xprev, uprev = sc.platoon_scenarios(S, A, HORIZON, cfg["dt"], track, seed0=seed0)
         idx, cnt = sc.topology(A, topo, nn=nn)
-        dm = ShardedDMPC(eng, S, A, idx, cnt, x0, xprev, uprev, rank=r, world=w, end_s=1e9)  # synthetic run: no end of track
+        dm = ShardedDMPC(eng, S, A, idx, cnt, x0, xprev, uprev, rank=r, world=w, end_s=1e9, group=group)  # synthetic run: no end of track
         if not args.warm:
             eng.set_options(warm_start=0)
         made.append(dm)
@@ -528,6 +528,56 @@ def run_dmpc(args):
             dm.iterate()
         if not args.no_graph:
             dm.capture()
+
+    def pipelined(S_total, w, r, group_b, sync):
+        """The same scenarios as TWO independent groups, each with its own state, handle, CUDA graph, stream and (w > 1)
+        communicator, interleaved: while one group waits for its all-gather - i.e. for the slowest rank's hardest QP of
+        that group - the other group's solve has the GPU, and the tail of one solve kernel is filled by the bulk of the
+        other.  Every scenario still does one solve and one exchange per iteration; the iterations of a group stay in
+        order.  Times `steps` iterations of ALL scenarios between two synchronisations (no L2 flush in between)."""
+        half = S_total // 2
+        sa, sb = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        grp = []
+        for st_, seed, g in ((sa, 0, None), (sb, half, group_b)):
+            with torch.cuda.stream(st_):
+                e_, d_ = make(half, A, w, r, seed0=seed, group=g)
+                settle(d_, args.settle)
+            grp.append((st_, e_, d_, torch.zeros((5,), dtype=torch.float64, device=dev)))
+        torch.cuda.synchronize()
+
+        def run(n, count):
+            main = torch.cuda.current_stream(dev)
+            sync()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(main)
+            for st_, _, _, _ in grp:
+                st_.wait_stream(main)
+            for _ in range(n):
+                for st_, _, d_, acc_ in grp:
+                    with torch.cuda.stream(st_):
+                        d_.iterate()
+                        if count:
+                            stt = d_.out["status"]
+                            runm = (d_.stop == 0).repeat_interleave(d_.a_local)
+                            feas = (stt == 1) | (stt == 2) | (stt == -2)
+                            brk = torch.zeros_like(runm)
+                            for v in FAIL_STATUS:
+                                brk |= stt == v
+                            acc_ += torch.stack([runm.sum().double(), (runm & (stt == 1)).sum().double(), (runm & (stt == 2)).sum().double(),
+                                                 (runm & ~feas).sum().double(), (runm & brk).sum().double()])
+            for st_, _, _, _ in grp:
+                main.wait_stream(st_)
+            e1.record(main)
+            torch.cuda.synchronize()
+            sync()
+            return e0.elapsed_time(e1)
+
+        run(W, False)
+        ms_tot = run(args.steps, True)
+        cnt = sum(g[3] for g in grp).cpu().numpy()
+        for _, e_, d_, _ in grp:
+            d_.release()
+        return ms_tot, cnt
 
     A = 16
     # ---- the same workload on ONE GPU (rank 0 alone, no collective), in the same run: the weak-scaling baseline
@@ -542,6 +592,9 @@ def run_dmpc(args):
                     "qp_timed": int(c1[0]), "not_feasible": int(c1[3]), "breakdowns": int(c1[4]), "e2e_value": c1[0] / float(w1.sum()),
                     "what": "256 scenarios x 16-agent chain platoons on rank 0 alone, same settle / warm-up / steps"}
             e1.close()
+            if args.pipelined:
+                msp1, cp1 = pipelined(256, 1, 0, None, torch.cuda.synchronize)
+                weak["pipelined_value"] = float(cp1[0]) / (msp1 * 1e-3)
         barrier()
     S = 256 * world
     eng, dm = make(S, A, world, rank)
@@ -566,6 +619,22 @@ def run_dmpc(args):
     coll = None
     if world > 1:
         coll = float(np.mean(_time_calls(torch, dm.exchange, 50)))
+    pipe = None
+    if args.pipelined:
+        gb = dist.new_group(ranks=list(range(world))) if world > 1 else None
+        msp, cp = pipelined(S, world, rank, gb, barrier)
+        tp = torch.tensor([msp], dtype=torch.float64, device=dev)
+        cpt = torch.tensor(cp, dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+            dist.all_reduce(cpt)
+        cpn = cpt.cpu().numpy()
+        pipe = {"value": float(cpn[0]) / (float(tp.item()) * 1e-3), "unit": "QP/s", "ms_per_iteration": float(tp.item()) / args.steps,
+                "qp_timed": int(cpn[0]), "solved": int(cpn[1]), "solved_inaccurate": int(cpn[2]), "not_feasible": int(cpn[3]),
+                "breakdowns": int(cpn[4]),
+                "what": "the same scenarios as two independent groups (own state, handle, CUDA graph, stream, communicator) "
+                        "interleaved on two streams; %d iterations of every scenario between two synchronisations, max over "
+                        "ranks, no L2 flush in between" % args.steps}
     # ---- reduce over ranks: a step is as slow as its slowest rank
     t = torch.tensor(np.concatenate([ms, walls * 1e3]), dtype=torch.float64, device=dev)
     cnts = torch.tensor(list(cn) + [ph[0], ph[1], ph[2]], dtype=torch.float64, device=dev)
@@ -642,6 +711,11 @@ def run_dmpc(args):
                 "solved_per_rank": [int(v) for v in allc[:, 1]], "qp_timed_per_rank": [int(v) for v in allc[:, 0]],
                 "ipm_iters_mean": float(allc[:, 5].sum()) / max(qp_timed, 1), "polish_rounds_mean": float(allc[:, 6].sum()) / max(qp_timed, 1),
                 "config3": config3}
+        if pipe is not None:
+            if weak and weak.get("pipelined_value"):
+                pipe["weak_baseline_pipelined"] = weak["pipelined_value"]
+                pipe["efficiency_same_workload"] = pipe["value"] / (world * weak["pipelined_value"])
+            line["pipelined"] = pipe
         print(json.dumps(line))
     rc = 3 if (breakdowns or not_feasible > 0.01 * qp_timed) else 0
     if rc:
@@ -674,6 +748,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true", help="N=1: skip the horizon sweep (config 4)")
     ap.add_argument("--no-config3", action="store_true", help="DMPC workload: skip the 64-vehicle platoon lines (config 3)")
+    ap.add_argument("--pipelined", action="store_true", help="DMPC workload: also time the scenarios as TWO interleaved groups on two streams (extra key `pipelined`)")
     ap.add_argument("--no-graph", action="store_true", help="DMPC workload: launch the iteration eagerly instead of as a CUDA graph")
     ap.add_argument("--quick", action="store_true", help="smaller sweep batches (development)")
     ap.add_argument("--warm", type=int, default=1, help="0: dmpc_options.warm_start off")
