@@ -29,7 +29,7 @@ Q3D int pass_update3(const Ctx3& c, double& v_out, double& lm_out, double& dl_ou
     c.res[j] = res; c.lam[j] = l;
     dl = fmax(dl, fabs(dr)); lm = fmax(lm, fabs(l));
     if (!(fabs(res) < 1e300) || !(fabs(l) < 1e300)) bad = 1;
-    if (D > 0.0) v = fmax(v, fabs(res) / (1.0 + babs));
+    if (D > 0.0) v = fmax(v, fabs(res) * q3_rcp(1.0 + babs));
   };
   Q3_FOR(k, c.N) {
     const double* xk = c.x + 9 * k;
@@ -264,8 +264,8 @@ Q3D double ipm_row_steps3(const Ctx3& c, const int corrector, const double smu) 
     if (corrector) dl = -((fma(c.dtt[j], c.dlam[j], l * t) - smu) + l * dt) * q3_rcp(t);
     else dl = -(l + c.D[j] * dt);
     c.dtt[j] = dt; c.dlam[j] = dl;
-    if (fma(a, dt, t) < 0.0) a = -t / dt;   // dt < 0 and -t / dt < a
-    if (fma(a, dl, l) < 0.0) a = -l / dl;
+    if (fma(a, dt, t) < 0.0) a = -t * q3_rcp(dt);   // dt < 0 and -t / dt < a
+    if (fma(a, dl, l) < 0.0) a = -l * q3_rcp(dl);
   };
   Q3_FOR(k, c.N) {
     const double* dk = c.dx + 9 * k;
