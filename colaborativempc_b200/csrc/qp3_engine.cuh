@@ -408,7 +408,7 @@ Q3D void stage_weights3(const Ctx3& c) {
     const double s11 = Qs2[4] + d[2] + d[3], s12 = Qs2[5], s22 = Qs2[8] + sd;
     const double c00 = s11 * s22 - s12 * s12, c01 = s02 * s12 - s01 * s22, c02 = s01 * s12 - s02 * s11;
     const double c11 = s00 * s22 - s02 * s02, c12 = s01 * s02 - s00 * s12, c22 = s00 * s11 - s01 * s01;
-    const double idet = 1.0 / (s00 * c00 + s01 * c01 + s02 * c02);
+    const double idet = q3_rcp(s00 * c00 + s01 * c01 + s02 * c02);
     double* si = c.Si + 6 * t;
     si[0] = c00 * idet; si[1] = c01 * idet; si[2] = c02 * idet; si[3] = c11 * idet; si[4] = c12 * idet; si[5] = c22 * idet;
     double* bh = c.bh + 4 * t;
@@ -443,7 +443,7 @@ enum { G3_ALM = 0, G3_AFF = 1, G3_COR = 2, G3_LAG = 3 };
 Q3D double row_w3(const Ctx3& c, int j, int mode, double smu) {
   if (mode == G3_ALM) return fma(c.D[j], c.res[j], c.lam[j]);
   if (mode == G3_AFF) return c.D[j] * (c.res[j] + c.tt[j]);
-  if (mode == G3_COR) return fma(c.D[j], c.res[j] + c.tt[j], (smu - c.dtt[j] * c.dlam[j]) / c.tt[j]);
+  if (mode == G3_COR) return fma(c.D[j], c.res[j] + c.tt[j], (smu - c.dtt[j] * c.dlam[j]) * q3_rcp(c.tt[j]));
   return c.lam[j];
 }
 

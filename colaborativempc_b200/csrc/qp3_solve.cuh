@@ -194,14 +194,6 @@ Q3N int pdas3(int rounds, int first, int bail, int bail_from) {
   return 0;
 }
 
-// largest alpha in (0, 1] with x + alpha dx >= 0 over the valid rows
-Q3D double step_to_boundary3(const Ctx3& c, const double* x, const double* dx) {
-  double a = 1.0;
-  Q3_FOR(j, c.RT)
-    if (row_ok3(c, j) && dx[j] < 0.0) a = fmin(a, -x[j] / dx[j]);
-  return q3_wmin(a);
-}
-
 // interior-point iterate (x, u, sigma, lambda, t) <-> the QP's global scratch slice.  Ends with a barrier.
 Q3D void ipm_park3(const Ctx3& c, double* park, int save) {
   double* const v[5] = {c.x, c.u, c.sig, c.lam, c.tt};
@@ -295,6 +287,7 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
   Hdr3* hd = c.hd;
   const int ipm_max = hd->ipm_max;
   const int m = c.N * (4 + c.cnt) + 4 * c.N;
+  const double inv_rows = 1.0 / (double)m;
   double lin = 1.0;  // product of (1 - alpha): scale of the linear residuals relative to the phase's start
   if (warm) {
     ipm_park3(c, park, 0);
@@ -342,7 +335,7 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
       for (int q = 0; q < hd->nq; ++q) { const int e = hd->nzl[q], i = hd->tri[e] >> 4; if (i == (hd->tri[e] & 15)) v_obj += xk[i] * (0.5 * hd->Q2u[e] * xk[i]); }
       v_obj += hd->q0 * xk[0];
     }
-    const double mu = q3_wsum(v_mu) / m;
+    const double mu = q3_wsum(v_mu) * inv_rows;
     const double rp = q3_wmax(v_rp), lmax = q3_wmax(v_lm);
     const double obj = fabs(q3_wsum(v_obj));
     const double rd = lin * rd0;
@@ -355,8 +348,8 @@ Q3N int ipm3(double mu_tol, int warm, double* park) {
     const double aa = ipm_row_steps3(c, 0, 0.0);
     double v_aff = 0.0;
     Q3_FOR(j, c.RT) v_aff = fma(c.lam[j] + aa * c.dlam[j], c.tt[j] + aa * c.dtt[j], v_aff);
-    const double mu_aff = q3_wsum(v_aff) / m;
-    const double sr = mu_aff / mu, smu = sr * sr * sr * mu;
+    const double mu_aff = q3_wsum(v_aff) * inv_rows;
+    const double sr = mu_aff * q3_rcp(mu), smu = sr * sr * sr * mu;
     // ---- corrector: same factor, full right-hand side with the second-order term (smu - dt_aff dlam_aff) / t
     affine_solve3(G3_COR, smu);
     const double al = fmin(1.0, 0.99 * ipm_row_steps3(c, 1, smu));
