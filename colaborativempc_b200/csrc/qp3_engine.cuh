@@ -574,15 +574,21 @@ Q3D void ric_factor_backward3(const Ctx3& c, const int defects) {
     const int e = Q3_LOCAL_E(q), ij = hd->tri[e];
     t_i[q] = ij >> 4; t_j[q] = ij & 15; t_w[q] = hd->wix[e] != 255 ? hd->wix[e] : -1; t_q[q] = hd->Q2u[e];
   }
-  Q3_ITEM(e, 45) {
-    const int ij = hd->tri[e], i = ij >> 4, j = ij & 15;
-    const double v = qt3(c, N - 1, e);
-    Pf[i * 9 + j] = v; Pf[j * 9 + i] = v;
+  {  // terminal cost-to-go: the cost of x_N (straight-line like the phases below, tables from the registers above)
+    const double* wN = c.Weff + 10 * (N - 1);
+    Q3_PRED2(e, 45) {
+      const int i = Q3_LOCAL_AT(t_i, e), j = Q3_LOCAL_AT(t_j, e), w = Q3_LOCAL_AT(t_w, e);
+      const double v = Q3_LOCAL_AT(t_q, e) + (w >= 0 ? wN[w >= 0 ? w : 0] : 0.0);
+      if (e_ok) { Pf[i * 9 + j] = v; Pf[j * 9 + i] = v; }
+    }
+    Q3_PRED(e, 18) { if (e_ok) Pf[81 + e] = 0.0; }
+    Q3_PRED(e, 9) {
+      const double g = c.gx[9 * (N - 1) + e], dd = defects ? c.dlam[9 * (N - 1) + e] : 0.0;
+      if (e_ok) { px[e] = g; hd->dbuf[(N - 1) & 1][e] = dd; hd->dbuf[N & 1][e] = 0.0; }
+    }
+    Q3_PREDS(l, 9, 13) { if (l_ok) hd->Pvv[l - 9] = 0.0; }
+    Q3_PREDS(l, 13, 15) { if (l_ok) pv[l - 13] = 0.0; }
   }
-  Q3_ITEM(e, 18) Pf[81 + e] = 0.0;
-  Q3_ITEM(e, 4) hd->Pvv[e] = 0.0;
-  Q3_ITEM(e, 9) { px[e] = c.gx[9 * (N - 1) + e]; hd->dbuf[(N - 1) & 1][e] = defects ? c.dlam[9 * (N - 1) + e] : 0.0; hd->dbuf[N & 1][e] = 0.0; }
-  Q3_ITEM(e, 2) pv[e] = 0.0;
   Q3_SYNC();
 #pragma unroll 1
   for (int k = N - 1; k >= 0; --k) {

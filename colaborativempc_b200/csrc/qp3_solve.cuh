@@ -18,10 +18,10 @@
 // the stage's rows at the current iterate (as eval_residuals3), lam += D res, and the pass statistics: v = how far the
 // active rows are from their bounds (relative), lm = max |lam|, dl = max |D res| (the multiplier update), bad = non-finite.
 // All lanes return the reduced values.  Ends with a barrier.
-Q3D int pass_update3(const Ctx3& c, double& v_out, double& lm_out, double& dl_out) {
+Q3D int pass_update3(const Ctx3& c, double& v_out, double& lm_out, double& dl_out, double& vin_out, double& lmin_out) {
   const double* lim = c.hd->lim;
   const double hm = 0.5 * c.hd->mind;
-  double v = 0.0, lm = 0.0, dl = 0.0;
+  double v = 0.0, lm = 0.0, dl = 0.0, vin = 0.0, lmin = 0.0;
   int bad = 0;
   auto row = [&](int j, double res, double babs) {
     const double D = c.D[j];
@@ -29,7 +29,10 @@ Q3D int pass_update3(const Ctx3& c, double& v_out, double& lm_out, double& dl_ou
     c.res[j] = res; c.lam[j] = l;
     dl = fmax(dl, fabs(dr)); lm = fmax(lm, fabs(l));
     if (!(fabs(res) < 1e300) || !(fabs(l) < 1e300)) bad = 1;
-    if (D > 0.0) v = fmax(v, fabs(res) * q3_rcp(1.0 + babs));
+    // what judging the guess needs, gathered in the same pass: the worst violation of a row outside the guess (relative
+    // to 1 + |b|; only violated rows pay the reciprocal) and the most negative multiplier inside it
+    if (D > 0.0) { v = fmax(v, fabs(res) * q3_rcp(1.0 + babs)); lmin = fmin(lmin, l); }
+    else if (res > 0.0) vin = fmax(vin, res * q3_rcp(1.0 + babs));
   };
   Q3_FOR(k, c.N) {
     const double* xk = c.x + 9 * k;
@@ -55,7 +58,7 @@ Q3D int pass_update3(const Ctx3& c, double& v_out, double& lm_out, double& dl_ou
     row(jb + 2, u1 - lim[4], fabs(lim[4])); row(jb + 3, -u1 - lim[5], fabs(lim[5]));
   }
   bad = q3_wor(bad);
-  v_out = q3_wmax(v); lm_out = q3_wmax(lm); dl_out = q3_wmax(dl);
+  v_out = q3_wmax(v); lm_out = q3_wmax(lm); dl_out = q3_wmax(dl); vin_out = q3_wmax(vin); lmin_out = q3_wmin(lmin);
   Q3_SYNC();
   return bad;
 }
@@ -115,8 +118,8 @@ Q3N int polish_round3(int first) {
 #pragma unroll 1
   for (;;) {
     // residuals, multiplier update, then: how far are the active rows from their bounds, is the guess still plausible
-    double v, lm, dl;
-    if (pass_update3(c, v, lm, dl)) return 2;
+    double v, lm, dl, vin, lmin;
+    if (pass_update3(c, v, lm, dl, vin, lmin)) return 2;
     lm = 1.0 + lm;
 #ifdef QP3_TRACE
     { double dl = 0; for (int j = 0; j < c.RT; ++j) dl = fmax(dl, fabs(c.D[j] * c.res[j])); int na = 0; for (int j = 0; j < c.RT; ++j) na += c.act[j];
@@ -137,7 +140,7 @@ Q3N int polish_round3(int first) {
     // ... and while the active rows are still far from their bounds (multipliers of 1e7 and more leave them 1e-2 off
     // after the first pass) neither the other rows' residuals nor the multipliers' signs mean anything yet: refine first
     const bool judge = tight || v <= 1e-4 || last;
-    const int changed = judge ? judge_rows3(c, tol, lm, 0) : 0;
+    const int changed = judge && (vin > tol || lmin < -tol * lm);  // = judge_rows3(c, tol, lm, 0), from the pass's own statistics
     if (tight && !changed) return 1;
     if (changed || last) {
       // update the guess with the tight thresholds (a row the loose test let through still moves)
